@@ -1,0 +1,221 @@
+/* pokeai_b200 -- C ABI of the B200-native decision hot path.
+ *
+ * Everything select766/pokeai does between "an observation arrives" and "an action
+ * index leaves" (plus the DQN minibatch update of the same network) is exposed here as
+ * plain-C entry points: extern "C", raw pointers and sizes, integer status returns.
+ * There are no torch / C++ types in any signature, so the reference's Python can bind
+ * it with ctypes (INTEGRATION.md shows the stub) and any other host with its FFI.
+ *
+ * The reference has no native interface (it is pure Python + numpy + torch-CPU); each
+ * entry point therefore cites the Python function(s) it replaces, relative to the
+ * reference checkout:
+ *
+ *   pk_encode        pokeai/ai/generic_move_model/feature_extractor.py:40-52
+ *                    (-> state_feature_extractor.py:92-197, choice_to_vec.py:40-61)
+ *   pk_mlp_forward   pokeai/ai/generic_move_model/mlp_model.py:21-30 called from
+ *                    agent.py:23-30 (_calc_q_vector / _calc_q_vector_batch)
+ *   pk_select        agent.py:32-45 (_act_by_model / _act_random), agent_train.py:30-33
+ *   pk_decide        agent_val.py:8-11 / agent_train.py:24-37: transform + forward + select
+ *   pk_dqn_*         trainer.py:152-198 (_update, _target_update)
+ *
+ * Conventions
+ *   - Return value 0 == PK_OK; anything else is an error and pk_last_error() (thread
+ *     local) describes it.  No C++ exception crosses this boundary.
+ *   - `stream` arguments are a cudaStream_t passed as void* (NULL = legacy default
+ *     stream).  Kernels are enqueued, never synchronised, unless the name ends in _host.
+ *   - Device buffers are owned by the caller.  The library never allocates per call and
+ *     never frees caller memory; the only allocations are inside pk_session_create.
+ *   - All multi-byte fields are little-endian; all float data is IEEE fp32.
+ */
+#ifndef POKEAI_B200_H
+#define POKEAI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PK_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define PK_API __attribute__((visibility("default")))
+#else
+#define PK_API
+#endif
+
+#define PK_OK 0
+#define PK_ERR_INVALID 1      /* bad argument (null pointer, size, alignment, unsupported shape) */
+#define PK_ERR_CUDA 2         /* a CUDA runtime call failed; message holds cudaGetErrorString */
+#define PK_ERR_NOT_INIT 3     /* pk_init has not been called on the current device */
+#define PK_ERR_UNSUPPORTED 4  /* valid request that this build has no kernel for */
+
+#define PK_MAX_ACTIONS 9   /* 4 moves + 5 switches (party of 6): feature_extractor.py:30-38 */
+#define PK_MAX_MOVES 4
+#define PK_N_STATE 50      /* state_feature_extractor.py:74-90 */
+#define PK_N_TYPES 17      /* state_feature_extractor.py:9-27 */
+#define PK_MAX_LAYERS 8
+#define PK_OBS_BYTES 144
+
+/* action flags */
+#define PK_FLAG_SWITCH 1u
+#define PK_FLAG_FORCE 2u
+
+/* One legal action (PossibleAction, pokeai/ai/common.py:7-14) with every string already
+ * replaced by its index in the reference's JSON tables. */
+typedef struct pk_action {
+  uint8_t flags;            /* PK_FLAG_SWITCH | PK_FLAG_FORCE */
+  uint8_t species;          /* index into all_pokemons.json */
+  uint8_t item;             /* index into all_items.json ('' is item 0) */
+  uint8_t n_moves;          /* 1 for a move action, <=4 (all moves of the target) for a switch */
+  uint16_t move[PK_MAX_MOVES]; /* indices into all_moves_with_hiddenpower_type.json */
+} pk_action;
+
+/* Packed observation: the fields of RLPolicyObservation that the encoder reads
+ * (rl_policy_observation.py:7-10, battle_status.py:41-188).  Index 0 of each pair is the
+ * friend side, 1 the opponent.  144 bytes, 16-byte aligned so that one battle is nine
+ * 16-byte loads. */
+typedef struct pk_obs {
+  uint8_t remaining[2];     /* SideStatus.remaining_pokes */
+  uint8_t total[2];         /* SideStatus.total_pokes (must be non-zero) */
+  uint16_t hp_cur[2];       /* ActivePokeStatus.hp_current */
+  uint16_t hp_max[2];       /* ActivePokeStatus.hp_max (must be non-zero) */
+  uint8_t status[2];        /* 0 none, 1..6 = psn,tox,par,brn,slp,frz, 7 = fnt/other (encodes to zeros) */
+  int8_t boost[2][7];       /* atk,def,spa,spd,spe,accuracy,evasion in -6..6 */
+  uint8_t opp_species;      /* opponent active species (its types come from the table) */
+  uint8_t weather;          /* 0 none, 1 SunnyDay, 2 RainDance, 3 Sandstorm */
+  uint8_t n_act;            /* number of legal actions; mask = first n_act slots */
+  uint8_t side_cond;        /* carried, never encoded (the reference does not encode it) */
+  pk_action act[PK_MAX_ACTIONS];
+  uint32_t user_tag;        /* opaque to the kernels */
+} pk_obs;
+
+/* Static tables (host pointers), copied to the device once by pk_init. */
+typedef struct pk_tables {
+  int32_t n_species;                 /* 251 */
+  int32_t n_moves;                   /* 267 */
+  int32_t n_items;                   /* 47  */
+  const uint32_t* species_type_mask; /* [n_species], bit t set = type t of the 17-type list */
+} pk_tables;
+
+/* MLPModel parameters in the reference's own (torch state_dict) layout, device pointers:
+ *   w[i]  = layers.{i}.weight  (n_channels, in_i, 1) row-major, in_0 = in_channels
+ *   b[i]  = layers.{i}.bias    (n_channels,)
+ *   w_out = output.weight      (1, n_channels, 1);  b_out = output.bias (1,)
+ * mlp_model.py:6-19 (bn=False; eval-mode BatchNorm must be folded by the caller). */
+typedef struct pk_mlp {
+  int32_t n_layers;
+  int32_t n_channels;
+  int32_t in_channels;
+  int32_t reserved;
+  const float* w[PK_MAX_LAYERS];
+  const float* b[PK_MAX_LAYERS];
+  const float* w_out;
+  const float* b_out;
+} pk_mlp;
+
+/* Action selection mode (agent.py:32-45, agent_train.py:30-33; softmax is a north-star
+ * extension with no reference counterpart). */
+#define PK_SELECT_ARGMAX 0   /* q[mask==0] = -inf; argmax, first maximum wins */
+#define PK_SELECT_EPSGREEDY 1 /* u_explore[b] < eps ? k-th legal slot, k = floor(u_pick[b]*n_legal) : argmax */
+#define PK_SELECT_SOFTMAX 2  /* inverse-CDF sample of softmax(q/temperature) over legal slots with u_pick[b] */
+
+typedef struct pk_select_params {
+  int32_t mode;
+  float eps;                 /* PK_SELECT_EPSGREEDY */
+  float temperature;         /* PK_SELECT_SOFTMAX */
+  int32_t reserved;
+  const float* u_explore;    /* [B] uniforms in [0,1) (device), EPSGREEDY only */
+  const float* u_pick;       /* [B] uniforms in [0,1) (device), EPSGREEDY and SOFTMAX */
+  float* probs;              /* optional [B*A] output of the softmax probabilities, or NULL */
+} pk_select_params;
+
+/* ---- library ------------------------------------------------------------------------ */
+PK_API int pk_abi_version(void);
+PK_API const char* pk_last_error(void);
+/* Upload the tables to `device` (cudaSetDevice is called).  Idempotent. */
+PK_API int pk_init(const pk_tables* tables, int device);
+/* Number of feature channels C = 50 + 2 + n_species + n_moves + n_items (617). */
+PK_API int pk_n_channels(void);
+/* Number of SMs of the initialised device (grid sizing information for callers). */
+PK_API int pk_sm_count(void);
+
+/* ---- weights -------------------------------------------------------------------------
+ * The kernels read a "prepared" copy of the network: every matrix transposed to
+ * (in, out) with the output width padded to a multiple of 32, all tensors in one
+ * contiguous fp32 buffer.  pk_mlp_prepared_floats gives its length; pk_mlp_prepare fills
+ * it from the state_dict layout (one small kernel; call again whenever weights change). */
+PK_API size_t pk_mlp_prepared_floats(int n_layers, int n_channels, int in_channels);
+PK_API int pk_mlp_prepare(const pk_mlp* mlp, float* prepared, void* stream);
+
+/* ---- the decision path -------------------------------------------------------------- */
+/* packed[B] -> feat (B, C, A) fp32, mask (B, A) int32.  feat must be 16-byte aligned.
+ * Replaces FeatureExtractor.transform, feature_extractor.py:40-52. */
+PK_API int pk_encode(const pk_obs* packed, int B, int A, float* feat, int32_t* mask, void* stream);
+
+/* Dense features (B, C, A) -> q (B, A).  Replaces MLPModel.forward as called by
+ * Agent._calc_q_vector[_batch], agent.py:23-30.  C must equal in_channels. */
+PK_API int pk_mlp_forward(const float* prepared, int n_layers, int n_channels, int in_channels,
+                   const float* feat, int B, int A, float* q, void* stream);
+
+/* q (B, A), mask (B, A) -> action (B,) int32.  Replaces agent.py:32-45. */
+PK_API int pk_select(const float* q, const int32_t* mask, int B, int A, const pk_select_params* sel,
+              int32_t* action, void* stream);
+
+/* One fused pass: packed[B] -> [feat (B,C,A)] [mask (B,A)] q (B,A) action (B,).
+ * feat and mask may be NULL (features are then never materialised).  Replaces
+ * AgentVal.act / AgentTrain.act's transform + _act_by_model / _act_random for a batch. */
+PK_API int pk_decide(const pk_obs* packed, int B, int A, const float* prepared, int n_layers, int n_channels,
+              float* feat, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
+              void* stream);
+
+/* ---- DQN update (trainer.py:152-198) --------------------------------------------------
+ * Transitions are held packed (two pk_obs per transition) and re-encoded on the fly.
+ * All pointers are device pointers.  Parameter / gradient / Adam-moment vectors use one
+ * flat fp32 layout in state_dict order (layers.0.weight, layers.0.bias, ...,
+ * output.weight, output.bias); pk_mlp_param_floats gives its length. */
+typedef struct pk_batch {
+  int32_t n;                 /* transitions in this (local) batch */
+  int32_t n_global;          /* divisor of the Huber sum: the global batch size (== n on one GPU) */
+  const pk_obs* state;       /* [n] */
+  const pk_obs* next_state;  /* [n]; ignored where terminal */
+  const int32_t* action;     /* [n] chosen slot */
+  const float* reward;       /* [n] */
+  const uint8_t* terminal;   /* [n] 1 = next_state is None */
+} pk_batch;
+
+PK_API size_t pk_mlp_param_floats(int n_layers, int n_channels, int in_channels);
+/* scratch floats pk_dqn_grad needs (per-CTA partial gradients) */
+PK_API size_t pk_dqn_scratch_floats(int n_layers, int n_channels, int in_channels);
+/* Forward x3, TD target, Huber, backward.  Writes grad (flat, pre-clamp, already divided by
+ * n_global) and adds this batch's loss contribution to *loss_sum (caller zeroes it).
+ * prepared_target is the prepared copy of the target network. */
+PK_API int pk_dqn_grad(const float* prepared, const float* prepared_target, int n_layers, int n_channels, int A,
+                const pk_batch* batch, float gamma, int double_dqn, float* grad, float* loss_sum,
+                float* scratch, void* stream);
+/* clamp(grad, -1, 1) then Adam (torch defaults, no weight decay) on the flat parameter
+ * vector, then refresh `prepared` from the new parameters.  step is 1-based. */
+PK_API int pk_clamp_adam(float* params, const float* grad, float* exp_avg, float* exp_avg_sq, int n_layers,
+                  int n_channels, int in_channels, float lr, float beta1, float beta2, float eps, int step,
+                  float* prepared, void* stream);
+
+/* ---- host-buffer session (for non-torch callers, and the end-to-end measurement) ------
+ * Owns device buffers for up to max_batch observations and one stream.  *_host calls copy
+ * packed observations host->device, run pk_decide, copy q / action back and synchronise. */
+typedef struct pk_session pk_session;
+PK_API int pk_session_create(pk_session** out, int max_batch, int A, int materialise_features);
+PK_API void pk_session_destroy(pk_session* s);
+/* weights given as HOST pointers in state_dict layout */
+PK_API int pk_session_load_weights(pk_session* s, const pk_mlp* host_mlp);
+PK_API int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
+                           float temperature, const float* u_explore_host, const float* u_pick_host,
+                           float* q_host, int32_t* action_host);
+/* device pointers of the session's last results (valid until the next call) */
+PK_API const float* pk_session_features(const pk_session* s);
+PK_API const int32_t* pk_session_mask(const pk_session* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POKEAI_B200_H */

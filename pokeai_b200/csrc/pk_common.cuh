@@ -1,0 +1,179 @@
+// Shared device/host definitions of the pokeai_b200 kernels (sm_100a only).
+//
+// Feature row order follows the reference bit for bit:
+//   state rows  0..49   pokeai/ai/state_feature_extractor.py:74-90,113-197
+//   choice rows 50..    pokeai/ai/generic_move_model/choice_to_vec.py:16-28,40-61
+//   assembly            pokeai/ai/generic_move_model/feature_extractor.py:40-52
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/pokeai_b200.h"
+
+static_assert(sizeof(pk_action) == 12, "pk_action must be 12 bytes");
+static_assert(sizeof(pk_obs) == PK_OBS_BYTES, "pk_obs must be 144 bytes");
+
+// ---- state block offsets (state_feature_extractor.py:42-48 order) -------------------------
+#define PK_ST_REMAINING 0
+#define PK_ST_TYPE 2
+#define PK_ST_HP 19
+#define PK_ST_NV 21
+#define PK_ST_RANK 33
+#define PK_ST_WEATHER 47
+// ---- choice block offsets relative to row PK_N_STATE (choice_to_vec.py:17-26) --------------
+#define PK_CH_SWITCH 0
+#define PK_CH_FORCE 1
+#define PK_CH_SPECIES 2
+
+// byte offsets inside pk_obs
+#define PK_OFF_REMAINING 0
+#define PK_OFF_TOTAL 2
+#define PK_OFF_HPCUR 4
+#define PK_OFF_HPMAX 8
+#define PK_OFF_STATUS 12
+#define PK_OFF_BOOST 14
+#define PK_OFF_OPP 28
+#define PK_OFF_WEATHER 29
+#define PK_OFF_NACT 30
+#define PK_OFF_ACT 32
+
+struct PkDeviceTables {
+  int n_species, n_moves, n_items;
+  int C;         // feature channels
+  int row_move;  // first move row   (absolute channel index)
+  int row_item;  // first item row
+  int pad0, pad1;
+  uint32_t type_mask[256];
+};
+
+// Layout of the prepared (transposed, padded) network, in floats.  HP = H rounded up to 32.
+//   w1t  [C+1][HP]  row k = input channel k, row C = zeros (target of "no row" gathers)
+//   b[0] [HP]
+//   wl[l] [HP][HP] (l = 1..n_layers-1), b[l] [HP]
+//   wout [HP], bout [4]
+struct PkLayout {
+  int C, H, HP, n_layers;
+  unsigned w1t, wout, bout, total;
+  unsigned b[PK_MAX_LAYERS];
+  unsigned wl[PK_MAX_LAYERS];
+};
+
+__host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
+  PkLayout L;
+  L.C = C;
+  L.H = H;
+  L.HP = (H + 31) & ~31;
+  L.n_layers = n_layers;
+  unsigned o = 0;
+  L.w1t = o;
+  o += (unsigned)(C + 1) * L.HP;
+  L.b[0] = o;
+  o += L.HP;
+  L.wl[0] = 0;
+  for (int l = 1; l < PK_MAX_LAYERS; ++l) {
+    if (l < n_layers) {
+      L.wl[l] = o;
+      o += (unsigned)L.HP * L.HP;
+      L.b[l] = o;
+      o += L.HP;
+    } else {
+      L.wl[l] = 0;
+      L.b[l] = 0;
+    }
+  }
+  L.wout = o;
+  o += L.HP;
+  L.bout = o;
+  o += 4;
+  L.total = o;
+  return L;
+}
+
+// Flat parameter vector in state_dict order (layers.i.weight, layers.i.bias, ..., output.weight, output.bias)
+struct PkParamLayout {
+  int C, H, n_layers;
+  unsigned w[PK_MAX_LAYERS], b[PK_MAX_LAYERS], wout, bout, total;
+};
+
+__host__ __device__ inline PkParamLayout pk_make_param_layout(int n_layers, int H, int C) {
+  PkParamLayout P;
+  P.C = C;
+  P.H = H;
+  P.n_layers = n_layers;
+  unsigned o = 0;
+  for (int l = 0; l < PK_MAX_LAYERS; ++l) {
+    if (l < n_layers) {
+      P.w[l] = o;
+      o += (unsigned)H * (l == 0 ? C : H);
+      P.b[l] = o;
+      o += H;
+    } else {
+      P.w[l] = 0;
+      P.b[l] = 0;
+    }
+  }
+  P.wout = o;
+  o += H;
+  P.bout = o;
+  o += 1;
+  P.total = o;
+  return P;
+}
+
+struct PkSelect {
+  int mode;
+  float eps;
+  float temperature;
+  const float* u_explore;
+  const float* u_pick;
+  float* probs;
+};
+
+// ---- small PTX helpers -----------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pk_smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+// generic-proxy writes to shared memory -> visible to the async proxy (TMA) that reads them next
+__device__ __forceinline__ void pk_fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// TMA 1-D bulk store shared -> global; size and both addresses multiples of 16
+__device__ __forceinline__ void pk_bulk_store(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(pk_smem_u32(ssrc)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void pk_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void pk_bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void pk_bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// TMA 1-D bulk load global -> shared, completion on an mbarrier
+__device__ __forceinline__ void pk_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pk_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void pk_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pk_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void pk_bulk_load(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   pk_smem_u32(sdst)),
+               "l"(gsrc), "r"(bytes), "r"(pk_smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void pk_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(pk_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void pk_fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+__device__ __forceinline__ float pk_ldg_f(const float* p) { return __ldg(p); }

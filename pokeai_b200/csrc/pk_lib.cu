@@ -1,0 +1,444 @@
+// C ABI of pokeai_b200 (see include/pokeai_b200.h).  Single translation unit: the kernels live in the
+// .cuh files included below so that the __constant__ tables are shared without -rdc.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "pk_common.cuh"
+#include "pk_decide.cuh"
+#include "pk_update.cuh"
+
+// ---- error handling -----------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int pk_fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define PK_CUDA(call)                                                                            \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) return pk_fail(PK_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+#define PK_REQUIRE(cond, ...) \
+  do {                        \
+    if (!(cond)) return pk_fail(PK_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- global state (one device per process, as in one-process-per-GPU deployments) -----------------
+struct PkGlobal {
+  int device = -1;
+  int sm_count = 0;
+  int max_smem = 0;
+  PkDeviceTables tab;
+  // tuning knobs of pk_decide (environment: PK_DECIDE_WARPS / PK_DECIDE_WRITERS / PK_DECIDE_NBUF / PK_ENCODE_WARPS)
+  int decide_warps = 12;
+  int decide_writers = 2;
+  int decide_nbuf = 2;
+  int encode_warps = 4;
+  int ctas_per_sm = 1;
+};
+static PkGlobal g;
+
+static int env_int(const char* name, int dflt, int lo, int hi) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  int x = atoi(v);
+  if (x < lo) x = lo;
+  if (x > hi) x = hi;
+  return x;
+}
+
+extern "C" int pk_abi_version(void) { return PK_ABI_VERSION; }
+extern "C" const char* pk_last_error(void) { return g_err; }
+
+extern "C" int pk_init(const pk_tables* t, int device) {
+  PK_REQUIRE(t != nullptr && t->species_type_mask != nullptr, "pk_init: null tables");
+  PK_REQUIRE(t->n_species > 0 && t->n_species <= 256, "pk_init: n_species %d not in 1..256 (u8 index)", t->n_species);
+  PK_REQUIRE(t->n_items > 0 && t->n_items <= 256, "pk_init: n_items %d not in 1..256 (u8 index)", t->n_items);
+  PK_REQUIRE(t->n_moves > 0 && t->n_moves <= 65536, "pk_init: n_moves %d not in 1..65536 (u16 index)", t->n_moves);
+  PK_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  PK_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return pk_fail(PK_ERR_UNSUPPORTED, "pk_init: device %d is sm_%d%d; this library is built for sm_100a only", device,
+                   prop.major, prop.minor);
+  memset(&g.tab, 0, sizeof(g.tab));
+  g.tab.n_species = t->n_species;
+  g.tab.n_moves = t->n_moves;
+  g.tab.n_items = t->n_items;
+  g.tab.row_move = PK_N_STATE + PK_CH_SPECIES + t->n_species;
+  g.tab.row_item = g.tab.row_move + t->n_moves;
+  g.tab.C = g.tab.row_item + t->n_items;
+  for (int i = 0; i < t->n_species; ++i) g.tab.type_mask[i] = t->species_type_mask[i] & ((1u << PK_N_TYPES) - 1u);
+  PK_CUDA(cudaMemcpyToSymbol(c_tab, &g.tab, sizeof(g.tab)));
+  g.device = device;
+  g.sm_count = prop.multiProcessorCount;
+  g.max_smem = (int)prop.sharedMemPerBlockOptin;
+  g.decide_warps = env_int("PK_DECIDE_WARPS", 12, 2, 16);
+  g.decide_writers = env_int("PK_DECIDE_WRITERS", 2, 1, 8);
+  g.decide_nbuf = env_int("PK_DECIDE_NBUF", 2, 1, PK_MAX_NBUF);
+  g.encode_warps = env_int("PK_ENCODE_WARPS", 4, 1, 8);
+  return PK_OK;
+}
+
+#define PK_CHECK_INIT() \
+  do {                  \
+    if (g.device < 0) return pk_fail(PK_ERR_NOT_INIT, "pk_init has not been called"); \
+  } while (0)
+
+extern "C" int pk_n_channels(void) { return g.device < 0 ? 0 : g.tab.C; }
+extern "C" int pk_sm_count(void) { return g.device < 0 ? 0 : g.sm_count; }
+
+// ---- weights --------------------------------------------------------------------------------------
+extern "C" size_t pk_mlp_prepared_floats(int n_layers, int n_channels, int in_channels) {
+  if (n_layers < 1 || n_layers > PK_MAX_LAYERS || n_channels < 1 || in_channels < 1) return 0;
+  return pk_make_layout(n_layers, n_channels, in_channels).total;
+}
+extern "C" size_t pk_mlp_param_floats(int n_layers, int n_channels, int in_channels) {
+  if (n_layers < 1 || n_layers > PK_MAX_LAYERS || n_channels < 1 || in_channels < 1) return 0;
+  return pk_make_param_layout(n_layers, n_channels, in_channels).total;
+}
+
+static int pk_prepare_impl(const pk_mlp* m, float* prepared, cudaStream_t st) {
+  const PkLayout lay = pk_make_layout(m->n_layers, m->n_channels, m->in_channels);
+  const int H = m->n_channels, HP = lay.HP, T = 256;
+  for (int l = 0; l < m->n_layers; ++l) {
+    PK_REQUIRE(m->w[l] != nullptr && m->b[l] != nullptr, "pk_mlp_prepare: null tensor in layer %d", l);
+    const int cin = l == 0 ? m->in_channels : H;
+    const int rows = l == 0 ? cin + 1 : HP;
+    float* dst = prepared + (l == 0 ? lay.w1t : lay.wl[l]);
+    const long long n = (long long)rows * HP;
+    pk_transpose_pad_kernel<<<(unsigned)((n + T - 1) / T), T, 0, st>>>(m->w[l], dst, H, cin, rows, HP);
+    pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->b[l], prepared + lay.b[l], H, HP);
+  }
+  PK_REQUIRE(m->w_out != nullptr && m->b_out != nullptr, "pk_mlp_prepare: null output tensor");
+  pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->w_out, prepared + lay.wout, H, HP);
+  pk_copy_pad_kernel<<<1, 32, 0, st>>>(m->b_out, prepared + lay.bout, 1, 4);
+  PK_CUDA(cudaGetLastError());
+  return PK_OK;
+}
+
+extern "C" int pk_mlp_prepare(const pk_mlp* m, float* prepared, void* stream) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(m != nullptr && prepared != nullptr, "pk_mlp_prepare: null argument");
+  PK_REQUIRE(m->n_layers >= 1 && m->n_layers <= PK_MAX_LAYERS, "pk_mlp_prepare: n_layers %d not in 1..%d", m->n_layers,
+             PK_MAX_LAYERS);
+  PK_REQUIRE(m->n_channels >= 1 && m->in_channels >= 1, "pk_mlp_prepare: bad channel counts");
+  PK_REQUIRE(aligned16(prepared), "pk_mlp_prepare: prepared buffer must be 16-byte aligned");
+  return pk_prepare_impl(m, prepared, (cudaStream_t)stream);
+}
+
+// ---- launch helpers ---------------------------------------------------------------------------------
+template <typename K>
+static int pk_set_smem(K kernel, unsigned bytes) {
+  PK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return PK_OK;
+}
+
+#define PK_DISPATCH_CPL_AT(CPL_, AT_, MACRO)                                 \
+  do {                                                                       \
+    if (CPL_ == 1 && AT_ == 4) { MACRO(1, 4); }                              \
+    else if (CPL_ == 1 && AT_ == 6) { MACRO(1, 6); }                         \
+    else if (CPL_ == 1 && AT_ == 9) { MACRO(1, 9); }                         \
+    else if (CPL_ == 2 && AT_ == 4) { MACRO(2, 4); }                         \
+    else if (CPL_ == 2 && AT_ == 6) { MACRO(2, 6); }                         \
+    else if (CPL_ == 2 && AT_ == 9) { MACRO(2, 9); }                         \
+    else if (CPL_ == 4 && AT_ == 4) { MACRO(4, 4); }                         \
+    else if (CPL_ == 4 && AT_ == 6) { MACRO(4, 6); }                         \
+    else if (CPL_ == 4 && AT_ == 9) { MACRO(4, 9); }                         \
+    else return pk_fail(PK_ERR_UNSUPPORTED, "no kernel for %d channels per lane / %d action slots", CPL_, AT_); \
+  } while (0)
+
+static inline int pk_at_for(int A) { return A <= 4 ? 4 : (A <= 6 ? 6 : 9); }
+
+static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepared, int n_layers, int n_channels,
+                          float* feat, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
+                          cudaStream_t st) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(B >= 0, "negative batch");
+  PK_REQUIRE(A >= 1 && A <= PK_MAX_ACTIONS, "A=%d not in 1..%d", A, PK_MAX_ACTIONS);
+  if (B == 0) return PK_OK;
+  PK_REQUIRE(packed != nullptr && aligned16(packed), "packed observations must be non-null and 16-byte aligned");
+  PK_REQUIRE(feat == nullptr || aligned16(feat), "feature buffer must be 16-byte aligned");
+  const bool with_mlp = prepared != nullptr;
+  PkLayout lay;
+  PkSelect ps;
+  memset(&ps, 0, sizeof(ps));
+  ps.temperature = 1.0f;
+  if (with_mlp) {
+    PK_REQUIRE(n_layers >= 1 && n_layers <= PK_MAX_LAYERS && n_channels >= 1, "bad network shape %d x %d", n_layers,
+               n_channels);
+    PK_REQUIRE(aligned16(prepared), "prepared weights must be 16-byte aligned");
+    PK_REQUIRE(q != nullptr || action != nullptr, "pk_decide: nothing to compute (q and action both null)");
+    lay = pk_make_layout(n_layers, n_channels, g.tab.C);
+    if (sel != nullptr) {
+      ps.mode = sel->mode;
+      ps.eps = sel->eps;
+      ps.temperature = sel->temperature;
+      ps.u_explore = sel->u_explore;
+      ps.u_pick = sel->u_pick;
+      ps.probs = sel->probs;
+      PK_REQUIRE(ps.mode >= PK_SELECT_ARGMAX && ps.mode <= PK_SELECT_SOFTMAX, "unknown selection mode %d", ps.mode);
+      if (ps.mode == PK_SELECT_EPSGREEDY)
+        PK_REQUIRE(ps.u_explore != nullptr && ps.u_pick != nullptr, "epsilon-greedy needs u_explore and u_pick");
+      if (ps.mode == PK_SELECT_SOFTMAX)
+        PK_REQUIRE(ps.u_pick != nullptr && ps.temperature > 0.0f, "softmax sampling needs u_pick and temperature > 0");
+    }
+  } else {
+    PK_REQUIRE(feat != nullptr || mask != nullptr, "pk_encode: nothing to compute (feat and mask both null)");
+    lay = pk_make_layout(1, 32, g.tab.C);
+  }
+  const int CPL = lay.HP / 32;
+  const int AT = pk_at_for(A);
+  int nwarps, n_writers, nbuf;
+  if (with_mlp) {
+    nwarps = g.decide_warps;
+    n_writers = feat != nullptr ? g.decide_writers : 0;
+    nbuf = feat != nullptr ? g.decide_nbuf : 1;
+    if (n_writers >= nwarps) n_writers = nwarps - 1;
+  } else {
+    nwarps = n_writers = g.encode_warps;
+    nbuf = feat != nullptr ? g.decide_nbuf : 1;
+  }
+  PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
+  while (plan.total > (unsigned)g.max_smem && nwarps > n_writers + 1) {  // drop MLP warps until the plan fits
+    --nwarps;
+    plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
+  }
+  while (plan.total > (unsigned)g.max_smem && (nbuf > 1 || n_writers > 1)) {
+    if (nbuf > 1) --nbuf;
+    else { --n_writers; if (!with_mlp) nwarps = n_writers; }
+    plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
+  }
+  if (plan.total > (unsigned)g.max_smem)
+    return pk_fail(PK_ERR_UNSUPPORTED,
+                   "network %d x %d does not fit the fused small-net kernel (%u B shared memory needed, %d available)",
+                   n_layers, n_channels, plan.total, g.max_smem);
+  const int grid = B < g.sm_count ? B : g.sm_count;
+  const uint4* pk = reinterpret_cast<const uint4*>(packed);
+#define PK_LAUNCH_DECIDE(C_, A_)                                                                              \
+  {                                                                                                           \
+    int rc_ = pk_set_smem(pk_decide_kernel<C_, A_>, plan.total);                                              \
+    if (rc_) return rc_;                                                                                      \
+    pk_decide_kernel<C_, A_><<<grid, nwarps * 32, plan.total, st>>>(pk, B, A, prepared, lay, feat, mask, q,   \
+                                                                    action, ps, n_writers, nbuf);             \
+  }
+  PK_DISPATCH_CPL_AT(CPL, AT, PK_LAUNCH_DECIDE);
+#undef PK_LAUNCH_DECIDE
+  PK_CUDA(cudaGetLastError());
+  return PK_OK;
+}
+
+extern "C" int pk_encode(const pk_obs* packed, int B, int A, float* feat, int32_t* mask, void* stream) {
+  return pk_decide_impl(packed, B, A, nullptr, 0, 0, feat, mask, nullptr, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int pk_decide(const pk_obs* packed, int B, int A, const float* prepared, int n_layers, int n_channels,
+                         float* feat, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
+                         void* stream) {
+  PK_REQUIRE(prepared != nullptr, "pk_decide: null prepared weights");
+  return pk_decide_impl(packed, B, A, prepared, n_layers, n_channels, feat, mask, q, action, sel, (cudaStream_t)stream);
+}
+
+extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channels, int in_channels, const float* feat,
+                              int B, int A, float* q, void* stream) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(B >= 0, "negative batch");
+  PK_REQUIRE(A >= 1 && A <= PK_MAX_ACTIONS, "A=%d not in 1..%d", A, PK_MAX_ACTIONS);
+  if (B == 0) return PK_OK;
+  PK_REQUIRE(prepared != nullptr && feat != nullptr && q != nullptr, "pk_mlp_forward: null argument");
+  PK_REQUIRE(aligned16(prepared), "prepared weights must be 16-byte aligned");
+  PK_REQUIRE(n_layers >= 1 && n_layers <= PK_MAX_LAYERS && n_channels >= 1 && in_channels >= 1, "bad network shape");
+  const PkLayout lay = pk_make_layout(n_layers, n_channels, in_channels);
+  const int CPL = lay.HP / 32, AT = pk_at_for(A);
+  const unsigned tail_bytes = (lay.total - lay.b[0]) * 4u;
+  const unsigned per_warp = ((unsigned)AT * lay.HP + (((unsigned)in_channels * A + 3u) & ~3u)) * 4u;
+  int nwarps = 8;
+  while (nwarps > 1 && tail_bytes + per_warp * nwarps > (unsigned)g.max_smem) --nwarps;
+  const unsigned smem = tail_bytes + per_warp * nwarps;
+  if (smem > (unsigned)g.max_smem)
+    return pk_fail(PK_ERR_UNSUPPORTED, "network %d x %d does not fit the small-net forward kernel", n_layers, n_channels);
+  int grid = (B + nwarps - 1) / nwarps;
+  if (grid > g.sm_count) grid = g.sm_count;
+  cudaStream_t st = (cudaStream_t)stream;
+#define PK_LAUNCH_DENSE(C_, A_)                                                                  \
+  {                                                                                              \
+    int rc_ = pk_set_smem(pk_dense_forward_kernel<C_, A_>, smem);                                \
+    if (rc_) return rc_;                                                                         \
+    pk_dense_forward_kernel<C_, A_><<<grid, nwarps * 32, smem, st>>>(feat, B, A, prepared, lay, q); \
+  }
+  PK_DISPATCH_CPL_AT(CPL, AT, PK_LAUNCH_DENSE);
+#undef PK_LAUNCH_DENSE
+  PK_CUDA(cudaGetLastError());
+  return PK_OK;
+}
+
+extern "C" int pk_select(const float* q, const int32_t* mask, int B, int A, const pk_select_params* sel,
+                         int32_t* action, void* stream) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(B >= 0, "negative batch");
+  PK_REQUIRE(A >= 1 && A <= PK_MAX_ACTIONS, "A=%d not in 1..%d", A, PK_MAX_ACTIONS);
+  if (B == 0) return PK_OK;
+  PK_REQUIRE(q != nullptr && mask != nullptr && action != nullptr, "pk_select: null argument");
+  PkSelect ps;
+  memset(&ps, 0, sizeof(ps));
+  ps.temperature = 1.0f;
+  if (sel != nullptr) {
+    ps.mode = sel->mode;
+    ps.eps = sel->eps;
+    ps.temperature = sel->temperature;
+    ps.u_explore = sel->u_explore;
+    ps.u_pick = sel->u_pick;
+    ps.probs = sel->probs;
+  }
+  PK_REQUIRE(ps.mode >= PK_SELECT_ARGMAX && ps.mode <= PK_SELECT_SOFTMAX, "unknown selection mode %d", ps.mode);
+  if (ps.mode == PK_SELECT_EPSGREEDY)
+    PK_REQUIRE(ps.u_explore != nullptr && ps.u_pick != nullptr, "epsilon-greedy needs u_explore and u_pick");
+  if (ps.mode == PK_SELECT_SOFTMAX)
+    PK_REQUIRE(ps.u_pick != nullptr && ps.temperature > 0.0f, "softmax sampling needs u_pick and temperature > 0");
+  pk_select_kernel<<<(B + 255) / 256, 256, 0, (cudaStream_t)stream>>>(q, mask, B, A, ps, action);
+  PK_CUDA(cudaGetLastError());
+  return PK_OK;
+}
+
+// ---- DQN update ---------------------------------------------------------------------------------------
+#include "pk_update_api.inc"
+
+// ---- host-buffer session ------------------------------------------------------------------------------
+struct pk_session {
+  int max_batch, A, materialise;
+  int n_layers, n_channels;
+  cudaStream_t stream;
+  pk_obs* d_packed;
+  float* d_feat;
+  int32_t* d_mask;
+  float* d_q;
+  int32_t* d_action;
+  float* d_u_explore;
+  float* d_u_pick;
+  float* d_params;
+  float* d_prepared;
+};
+
+extern "C" void pk_session_destroy(pk_session* s) {
+  if (!s) return;
+  cudaFree(s->d_packed);
+  cudaFree(s->d_feat);
+  cudaFree(s->d_mask);
+  cudaFree(s->d_q);
+  cudaFree(s->d_action);
+  cudaFree(s->d_u_explore);
+  cudaFree(s->d_u_pick);
+  cudaFree(s->d_params);
+  cudaFree(s->d_prepared);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  free(s);
+}
+
+extern "C" int pk_session_create(pk_session** out, int max_batch, int A, int materialise_features) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(out != nullptr, "pk_session_create: null out");
+  PK_REQUIRE(max_batch >= 1, "pk_session_create: max_batch must be positive");
+  PK_REQUIRE(A >= 1 && A <= PK_MAX_ACTIONS, "A=%d not in 1..%d", A, PK_MAX_ACTIONS);
+  pk_session* s = (pk_session*)calloc(1, sizeof(pk_session));
+  if (!s) return pk_fail(PK_ERR_INVALID, "out of host memory");
+  s->max_batch = max_batch;
+  s->A = A;
+  s->materialise = materialise_features;
+  cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+  const size_t nb = (size_t)max_batch;
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_packed, nb * sizeof(pk_obs));
+  if (e == cudaSuccess && materialise_features) e = cudaMalloc(&s->d_feat, nb * g.tab.C * A * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_mask, nb * A * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_q, nb * A * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_action, nb * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_u_explore, nb * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_u_pick, nb * sizeof(float));
+  if (e != cudaSuccess) {
+    pk_session_destroy(s);
+    return pk_fail(PK_ERR_CUDA, "pk_session_create: %s", cudaGetErrorString(e));
+  }
+  *out = s;
+  return PK_OK;
+}
+
+extern "C" int pk_session_load_weights(pk_session* s, const pk_mlp* hm) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(s != nullptr && hm != nullptr, "pk_session_load_weights: null argument");
+  PK_REQUIRE(hm->n_layers >= 1 && hm->n_layers <= PK_MAX_LAYERS && hm->n_channels >= 1, "bad network shape");
+  PK_REQUIRE(hm->in_channels == g.tab.C, "in_channels %d != feature channels %d", hm->in_channels, g.tab.C);
+  const PkParamLayout P = pk_make_param_layout(hm->n_layers, hm->n_channels, hm->in_channels);
+  const PkLayout lay = pk_make_layout(hm->n_layers, hm->n_channels, hm->in_channels);
+  cudaFree(s->d_params);
+  cudaFree(s->d_prepared);
+  s->d_params = s->d_prepared = nullptr;
+  PK_CUDA(cudaMalloc(&s->d_params, (size_t)P.total * sizeof(float)));
+  PK_CUDA(cudaMalloc(&s->d_prepared, (size_t)lay.total * sizeof(float)));
+  pk_mlp dm = *hm;
+  const int H = hm->n_channels;
+  for (int l = 0; l < hm->n_layers; ++l) {
+    PK_REQUIRE(hm->w[l] && hm->b[l], "null tensor in layer %d", l);
+    const size_t nw = (size_t)H * (l == 0 ? hm->in_channels : H);
+    PK_CUDA(cudaMemcpyAsync(s->d_params + P.w[l], hm->w[l], nw * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    PK_CUDA(cudaMemcpyAsync(s->d_params + P.b[l], hm->b[l], H * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    dm.w[l] = s->d_params + P.w[l];
+    dm.b[l] = s->d_params + P.b[l];
+  }
+  PK_REQUIRE(hm->w_out && hm->b_out, "null output tensor");
+  PK_CUDA(cudaMemcpyAsync(s->d_params + P.wout, hm->w_out, H * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+  PK_CUDA(cudaMemcpyAsync(s->d_params + P.bout, hm->b_out, sizeof(float), cudaMemcpyHostToDevice, s->stream));
+  dm.w_out = s->d_params + P.wout;
+  dm.b_out = s->d_params + P.bout;
+  int rc = pk_prepare_impl(&dm, s->d_prepared, s->stream);
+  if (rc) return rc;
+  PK_CUDA(cudaStreamSynchronize(s->stream));
+  s->n_layers = hm->n_layers;
+  s->n_channels = hm->n_channels;
+  return PK_OK;
+}
+
+extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
+                                      float temperature, const float* u_explore_host, const float* u_pick_host,
+                                      float* q_host, int32_t* action_host) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(s != nullptr && packed_host != nullptr, "pk_session_decide_host: null argument");
+  PK_REQUIRE(s->d_prepared != nullptr, "pk_session_decide_host: no weights loaded");
+  PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
+  if (B == 0) return PK_OK;
+  PK_CUDA(cudaMemcpyAsync(s->d_packed, packed_host, (size_t)B * sizeof(pk_obs), cudaMemcpyHostToDevice, s->stream));
+  pk_select_params sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.mode = mode;
+  sp.eps = eps;
+  sp.temperature = temperature;
+  if (mode == PK_SELECT_EPSGREEDY) {
+    PK_REQUIRE(u_explore_host != nullptr, "epsilon-greedy needs u_explore");
+    PK_CUDA(cudaMemcpyAsync(s->d_u_explore, u_explore_host, (size_t)B * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    sp.u_explore = s->d_u_explore;
+  }
+  if (mode != PK_SELECT_ARGMAX) {
+    PK_REQUIRE(u_pick_host != nullptr, "this selection mode needs u_pick");
+    PK_CUDA(cudaMemcpyAsync(s->d_u_pick, u_pick_host, (size_t)B * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    sp.u_pick = s->d_u_pick;
+  }
+  int rc = pk_decide_impl(s->d_packed, B, s->A, s->d_prepared, s->n_layers, s->n_channels, s->d_feat, s->d_mask, s->d_q,
+                          s->d_action, &sp, s->stream);
+  if (rc) return rc;
+  if (q_host) PK_CUDA(cudaMemcpyAsync(q_host, s->d_q, (size_t)B * s->A * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+  if (action_host)
+    PK_CUDA(cudaMemcpyAsync(action_host, s->d_action, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+  PK_CUDA(cudaStreamSynchronize(s->stream));
+  return PK_OK;
+}
+
+extern "C" const float* pk_session_features(const pk_session* s) { return s ? s->d_feat : nullptr; }
+extern "C" const int32_t* pk_session_mask(const pk_session* s) { return s ? s->d_mask : nullptr; }

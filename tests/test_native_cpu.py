@@ -1,0 +1,59 @@
+"""CPU: the C-ABI library builds for sm_100a, loads, and exports everything include/pokeai_b200.h declares.
+No compute call is made here (there is no GPU and no CPU fallback)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+
+def test_library_builds_loads_and_exports_header():
+    from pokeai_b200 import build as b
+    from pokeai_b200 import _native as N
+    path = b.build()
+    assert path.exists()
+    lib = N.lib()
+    declared = N.declared_symbols()
+    assert len(declared) >= 20
+    for s in declared:
+        assert hasattr(lib, s), f"{s} declared in the header but not exported"
+    assert set(N._SIGNATURES) == set(declared)
+    assert lib.pk_abi_version() == 1
+
+
+def test_layout_sizes():
+    from pokeai_b200 import _native as N
+    lib = N.lib()
+    # 43 777 parameters for the default network
+    assert lib.pk_mlp_param_floats(2, 64, 617) == 43777
+    assert lib.pk_mlp_param_floats(4, 2048, 617) == 13856769
+    assert lib.pk_mlp_prepared_floats(2, 64, 617) == (617 + 1) * 64 + 64 + 64 * 64 + 64 + 64 + 4
+    assert lib.pk_mlp_prepared_floats(3, 16, 617) == 618 * 32 + 32 + 2 * (32 * 32 + 32) + 32 + 4
+    assert lib.pk_mlp_prepared_floats(0, 64, 617) == 0
+
+
+def test_calls_fail_loudly_without_init_or_device():
+    import torch
+    from pokeai_b200 import _native as N
+    lib = N.lib()
+    if torch.cuda.is_available():
+        pytest.skip("covers the no-GPU behaviour")
+    rc = lib.pk_encode(None, 4, 9, None, None, None)
+    assert rc == 3 and b"pk_init" in lib.pk_last_error()
+    tm = np.zeros(251, dtype=np.uint32)
+    t = N.pk_tables(251, 267, 47, tm.ctypes.data_as(C.POINTER(C.c_uint32)))
+    rc = lib.pk_init(C.byref(t), 0)
+    assert rc == 2  # CUDA error: no device; never a silent CPU path
+    from pokeai_b200 import ops
+    with pytest.raises(ValueError):
+        ops.encode(torch.zeros((1, 144), dtype=torch.uint8), 9)
+
+
+def test_record_layout_matches_header():
+    """the numpy dtype of the host packer is byte-for-byte the C struct"""
+    from pokeai_b200.packed import PK_ACT_DTYPE, PK_OBS_DTYPE
+    off = {n: PK_OBS_DTYPE.fields[n][1] for n in PK_OBS_DTYPE.names}
+    assert off == {"remaining": 0, "total": 2, "hp_cur": 4, "hp_max": 8, "status": 12, "boost": 14, "opp_species": 28,
+                   "weather": 29, "n_act": 30, "side_cond": 31, "act": 32, "user_tag": 140}
+    aoff = {n: PK_ACT_DTYPE.fields[n][1] for n in PK_ACT_DTYPE.names}
+    assert aoff == {"flags": 0, "species": 1, "item": 2, "n_moves": 3, "move": 4}
+    assert PK_OBS_DTYPE.itemsize == 144
