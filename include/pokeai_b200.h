@@ -150,7 +150,7 @@ PK_API size_t pk_mlp_prepared_floats(int n_layers, int n_channels, int in_channe
 PK_API int pk_mlp_prepare(const pk_mlp* mlp, float* prepared, void* stream);
 
 /* ---- the decision path -------------------------------------------------------------- */
-/* packed[B] -> feat (B, C, A) fp32, mask (B, A) int32.  feat must be 16-byte aligned.
+/* packed[B] -> feat (B, C, A) fp32, mask (B, A) int32.  feat must be 4-byte aligned.
  * Replaces FeatureExtractor.transform, feature_extractor.py:40-52. */
 PK_API int pk_encode(const pk_obs* packed, int B, int A, float* feat, int32_t* mask, void* stream);
 

@@ -1,19 +1,21 @@
 // The decision kernel: packed observations -> [features] [mask] -> Q values -> action.
 //
-// One persistent CTA per SM, warps specialised by role, no block-level barrier after the
-// prologue:
+// One persistent CTA per SM; every warp takes one battle at a time and is independent of the others
+// (no block-level barrier after the prologue):
 //
-//   writer warps  materialise the (C, A) fp32 feature block of one battle at a time in a
-//                 shared-memory staging tile that is all zeros except for ~450 state values and
-//                 <= 72 one-hot pokes, hand it to the TMA engine as ONE bulk store
-//                 (cp.async.bulk shared -> global, 22 KB), and once the engine has read the tile
-//                 un-poke it instead of re-zeroing it.  HBM-write bound: 22 212 B per battle.
-//   MLP warps     never read the dense features.  Layer 1 is evaluated in gather form
-//                 (b1 + sum_k W1[:,k] s_k over the non-zero state values + the <= 8 one-hot rows of
-//                 each action column, read from the transposed weights through L1), the hidden
-//                 layers run out of shared-memory weights with 2 channels per lane and A columns
-//                 per lane in registers, the head is a warp butterfly, and the masked
-//                 argmax / epsilon-greedy / softmax draw is done in registers.
+//   parse     the 144-byte record is read once (nine 16-byte loads, prefetched one battle ahead),
+//             the 50 state values and the <= 72 one-hot rows are derived branch-free into the warp's
+//             shared-memory scratch.
+//   features  (optional) the (C, A) fp32 block of the battle is a 22 KB run of zeros with ~450 state
+//             values in front and <= 72 ones scattered behind.  The warp streams it straight from
+//             registers with coalesced 16-byte stores (zeros need no staging), then pokes the ones.
+//             HBM-write bound: 22 212 B per battle.
+//   MLP       never reads the dense features.  Layer 0 is evaluated in gather form
+//             (b + sum_k W[:,k] s_k over the non-zero state values + the <= 8 one-hot rows of each
+//             action column, fetched from the transposed weights through L1); the hidden layers run out
+//             of shared-memory weights with the lane owning adjacent output channels and all A columns,
+//             using packed fp32x2 FMAs (FFMA2); the head is a warp butterfly; the masked argmax /
+//             epsilon-greedy / softmax draw happens in registers.
 //
 // Reference semantics being restated (bit-exact for features and masks):
 //   FeatureExtractor.transform           feature_extractor.py:40-52
@@ -29,72 +31,57 @@
 
 __constant__ PkDeviceTables c_tab;
 
-#define PK_WARP_REC_BYTES 576   // up to 4 records of 144 B (one per staging slot)
-#define PK_WARP_SV_BYTES 256    // 64 floats: the 50 state values
+#define PK_WARP_REC_BYTES 144   // the record being processed
+#define PK_WARP_SV_BYTES 256    // 64 floats: the 50 state values, zero padded
 #define PK_WARP_IDX_BYTES 320   // 80 ints: gather rows, 8 per action column
-#define PK_MAX_NBUF 4
+#define PK_WARP_FIXED_BYTES (PK_WARP_REC_BYTES + PK_WARP_SV_BYTES + PK_WARP_IDX_BYTES)
 
 // ---- state features (state_feature_extractor.py:113-197) ----------------------------------------
-// r points at one 144-byte record in shared memory.  Python computes a/b in double and numpy stores
-// it as float32; IEEE fp32 division of two integers < 2^24 gives the same bits (double rounding is
-// innocuous for division when 53 >= 2*24+2), so __fdiv_rn is exact parity -- never __fdividef.
+// r points at one 144-byte record in shared memory.  Every feature is num/den of two small integers
+// (den = 1 for the one-hots).  Python computes a/b in double and numpy stores it as float32; IEEE fp32
+// division of two integers < 2^24 gives the same bits (double rounding is innocuous for division when
+// 53 >= 2*24+2), so one __fdiv_rn is exact parity -- never __fdividef.
 __device__ __forceinline__ float pk_state_feature(const uint8_t* r, int k) {
+  int num = 0, den = 1;
   if (k < PK_ST_TYPE) {  // :113-123 remaining / total
-    return __fdiv_rn((float)r[PK_OFF_REMAINING + k], (float)r[PK_OFF_TOTAL + k]);
+    num = r[PK_OFF_REMAINING + k];
+    den = r[PK_OFF_TOTAL + k];
   } else if (k < PK_ST_HP) {  // :125-138 opponent active's types
-    uint32_t tm = c_tab.type_mask[r[PK_OFF_OPP]];
-    return (float)((tm >> (k - PK_ST_TYPE)) & 1u);
+    num = (int)((c_tab.type_mask[r[PK_OFF_OPP]] >> (k - PK_ST_TYPE)) & 1u);
   } else if (k < PK_ST_NV) {  // :140-151 hp ratio
-    const uint16_t* hc = reinterpret_cast<const uint16_t*>(r + PK_OFF_HPCUR);
-    const uint16_t* hm = reinterpret_cast<const uint16_t*>(r + PK_OFF_HPMAX);
-    return __fdiv_rn((float)hc[k - PK_ST_HP], (float)hm[k - PK_ST_HP]);
+    num = reinterpret_cast<const uint16_t*>(r + PK_OFF_HPCUR)[k - PK_ST_HP];
+    den = reinterpret_cast<const uint16_t*>(r + PK_OFF_HPMAX)[k - PK_ST_HP];
   } else if (k < PK_ST_RANK) {  // :153-167 non-volatile condition one-hot
-    int side = (k - PK_ST_NV) / 6;
-    int cond = (k - PK_ST_NV) - 6 * side;
-    return r[PK_OFF_STATUS + side] == cond + 1 ? 1.0f : 0.0f;
+    const int side = (k >= PK_ST_NV + 6) ? 1 : 0;
+    num = r[PK_OFF_STATUS + side] == (k - PK_ST_NV - 6 * side) + 1 ? 1 : 0;
   } else if (k < PK_ST_WEATHER) {  // :169-182 (rank + 6) / 12
-    int bst = (int)(int8_t)r[PK_OFF_BOOST + (k - PK_ST_RANK)];
-    return __fdiv_rn((float)(bst + 6), 12.0f);
+    num = (int)(int8_t)r[PK_OFF_BOOST + (k - PK_ST_RANK)] + 6;
+    den = 12;
   } else if (k < PK_N_STATE) {  // :184-197 weather one-hot
-    return r[PK_OFF_WEATHER] == (k - PK_ST_WEATHER) + 1 ? 1.0f : 0.0f;
+    num = r[PK_OFF_WEATHER] == (k - PK_ST_WEATHER) + 1 ? 1 : 0;
   }
-  return 0.0f;
+  return __fdiv_rn((float)num, (float)den);
 }
 
 // ---- choice rows (choice_to_vec.py:40-61) -----------------------------------------------------
 // Slot t of action column c: 0 switch flag, 1 force_switch flag, 2 species, 3 item, 4..7 moves.
 // Returns the absolute feature row, or -1 when the slot is empty / out of table range / a repeat
 // of an earlier move of the same action (the reference sets the element to 1, it does not add).
+// Straight-line selects: the three action words are the same for the 8 lanes of a column.
 __device__ __forceinline__ int pk_choice_row(const uint8_t* r, int c, int t) {
-  const uint8_t* a = r + PK_OFF_ACT + 12 * c;
-  const uint32_t flags = a[0];
-  if (t == 0) return (flags & PK_FLAG_SWITCH) ? PK_N_STATE + PK_CH_SWITCH : -1;
-  if (t == 1) return (flags & PK_FLAG_FORCE) ? PK_N_STATE + PK_CH_FORCE : -1;
-  if (t == 2) {
-    int sp = a[1];
-    return sp < c_tab.n_species ? PK_N_STATE + PK_CH_SPECIES + sp : -1;
-  }
-  if (t == 3) {
-    int it = a[2];
-    return it < c_tab.n_items ? c_tab.row_item + it : -1;
-  }
-  const int mi = t - 4;
-  if (mi >= (int)a[3] || mi >= PK_MAX_MOVES) return -1;
-  const uint16_t* mv = reinterpret_cast<const uint16_t*>(a + 4);
-  const int m = mv[mi];
-  if (m >= c_tab.n_moves) return -1;
-  for (int e = 0; e < mi; ++e)
-    if (mv[e] == m) return -1;
-  return c_tab.row_move + m;
-}
-
-// write `val` at every one-hot position of the choice block; tile points at element (row 0, col 0)
-__device__ __forceinline__ void pk_poke_choice(float* tile, const uint8_t* r, int A, int n_act, int lane, float val) {
-  for (int e = lane; e < 8 * n_act; e += 32) {
-    const int c = e >> 3, t = e & 7;
-    const int row = pk_choice_row(r, c, t);
-    if (row >= 0) tile[row * A + c] = val;
-  }
+  const uint32_t* aw = reinterpret_cast<const uint32_t*>(r + PK_OFF_ACT) + 3 * c;
+  const uint32_t w0 = aw[0], w1 = aw[1], w2 = aw[2];
+  const uint32_t flags = w0 & 0xffu, sp = (w0 >> 8) & 0xffu, it = (w0 >> 16) & 0xffu, nm = w0 >> 24;
+  const uint32_t m0 = w1 & 0xffffu, m1 = w1 >> 16, m2 = w2 & 0xffffu, m3 = w2 >> 16;
+  const uint32_t mv = t == 4 ? m0 : t == 5 ? m1 : t == 6 ? m2 : m3;
+  const bool dup = (t >= 5 && mv == m0) || (t >= 6 && mv == m1) || (t == 7 && mv == m2);
+  const bool mv_ok = (uint32_t)(t - 4) < nm && mv < (uint32_t)c_tab.n_moves && !dup;
+  int row = mv_ok ? c_tab.row_move + (int)mv : -1;                                           // t >= 4
+  row = t == 0 ? ((flags & PK_FLAG_SWITCH) ? PK_N_STATE + PK_CH_SWITCH : -1) : row;
+  row = t == 1 ? ((flags & PK_FLAG_FORCE) ? PK_N_STATE + PK_CH_FORCE : -1) : row;
+  row = t == 2 ? (sp < (uint32_t)c_tab.n_species ? PK_N_STATE + PK_CH_SPECIES + (int)sp : -1) : row;
+  row = t == 3 ? (it < (uint32_t)c_tab.n_items ? c_tab.row_item + (int)it : -1) : row;
+  return row;
 }
 
 // ---- action selection (agent.py:32-45, agent_train.py:30-33) --------------------------------------
@@ -173,19 +160,80 @@ __device__ __forceinline__ int pk_select_dev(const float (&qv)[AT], uint32_t leg
   return idx;
 }
 
+// ---- vector helpers: the lane owns CPL adjacent channels, j = CPL * lane + i -------------------------
+template <int CPL>
+__device__ __forceinline__ void pk_ldg_vec(const float* __restrict__ row, int lane, float (&v)[CPL]) {
+  if constexpr (CPL == 1) {
+    v[0] = __ldg(row + lane);
+  } else if constexpr (CPL == 2) {
+    const float2 t = __ldg(reinterpret_cast<const float2*>(row) + lane);
+    v[0] = t.x;
+    v[1] = t.y;
+  } else {
+    static_assert(CPL == 4, "CPL must be 1, 2 or 4");
+    const float4 t = __ldg(reinterpret_cast<const float4*>(row) + lane);
+    v[0] = t.x;
+    v[1] = t.y;
+    v[2] = t.z;
+    v[3] = t.w;
+  }
+}
+template <int CPL>
+__device__ __forceinline__ void pk_lds_vec(const float* row, int lane, float (&v)[CPL]) {
+  if constexpr (CPL == 1) {
+    v[0] = row[lane];
+  } else if constexpr (CPL == 2) {
+    const float2 t = reinterpret_cast<const float2*>(row)[lane];
+    v[0] = t.x;
+    v[1] = t.y;
+  } else {
+    const float4 t = reinterpret_cast<const float4*>(row)[lane];
+    v[0] = t.x;
+    v[1] = t.y;
+    v[2] = t.z;
+    v[3] = t.w;
+  }
+}
+template <int CPL>
+__device__ __forceinline__ void pk_sts_vec(float* row, int lane, const float (&v)[CPL]) {
+  if constexpr (CPL == 1) {
+    row[lane] = v[0];
+  } else if constexpr (CPL == 2) {
+    reinterpret_cast<float2*>(row)[lane] = make_float2(v[0], v[1]);
+  } else {
+    reinterpret_cast<float4*>(row)[lane] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
+// acc[0..CPL) += w[0..CPL) * x   -- packed fp32x2 FMA (FFMA2, sm_100+) when the lane owns channel pairs;
+// each half is an IEEE fma.rn, identical to two scalar fmaf.
+template <int CPL>
+__device__ __forceinline__ void pk_fma_vec(float (&acc)[CPL], const float (&w)[CPL], float x) {
+  if constexpr (CPL == 1) {
+    acc[0] = fmaf(w[0], x, acc[0]);
+  } else {
+#pragma unroll
+    for (int p = 0; p < CPL; p += 2) {
+      unsigned long long a, ww, xx, d;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(acc[p]), "f"(acc[p + 1]));
+      asm("mov.b64 %0, {%1, %2};" : "=l"(ww) : "f"(w[p]), "f"(w[p + 1]));
+      asm("mov.b64 %0, {%1, %1};" : "=l"(xx) : "f"(x));
+      asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(ww), "l"(xx), "l"(a));
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[p]), "=f"(acc[p + 1]) : "l"(d));
+    }
+  }
+}
+
 // ---- shared-memory plan ---------------------------------------------------------------------------
 struct PkSmemPlan {
   unsigned tail;         // prepared floats from lay.b[0] to lay.total (biases, hidden weights, head)
   unsigned w1s;          // first PK_N_STATE rows of W1^T
   unsigned warp_area;    // per-warp scratch
   unsigned warp_stride;
-  unsigned staging;      // writer staging tiles
-  unsigned lbuf;         // floats per staging tile
   unsigned total;
 };
 
-__host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, int nwarps, int n_writers, int nbuf,
-                                                   int A, bool with_mlp) {
+__host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, int nwarps, bool with_mlp) {
   PkSmemPlan p;
   unsigned o = 0;
   p.tail = o;
@@ -193,12 +241,8 @@ __host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, 
   p.w1s = o;
   if (with_mlp) o += (unsigned)PK_N_STATE * lay.HP * 4u;
   p.warp_area = o;
-  p.warp_stride = PK_WARP_REC_BYTES + PK_WARP_SV_BYTES + PK_WARP_IDX_BYTES + (with_mlp ? (unsigned)AT * lay.HP * 4u : 0u);
+  p.warp_stride = PK_WARP_FIXED_BYTES + (with_mlp ? (unsigned)AT * lay.HP * 4u : 0u);
   o += p.warp_stride * nwarps;
-  o = (o + 127u) & ~127u;
-  p.staging = o;
-  p.lbuf = ((unsigned)lay.C * A + 3u + 3u) & ~3u;
-  o += p.lbuf * 4u * n_writers * nbuf;
   p.total = o;
   return p;
 }
@@ -209,16 +253,16 @@ __device__ __forceinline__ void pk_hidden_layer(const float* __restrict__ WT, co
                                                 float* hbuf, float (&h)[AT][CPL], int lane) {
   constexpr int HP = 32 * CPL;
 #pragma unroll
-  for (int c = 0; c < AT; ++c)
-#pragma unroll
-    for (int i = 0; i < CPL; ++i) hbuf[c * HP + lane + 32 * i] = h[c][i];
+  for (int c = 0; c < AT; ++c) pk_sts_vec<CPL>(hbuf + c * HP, lane, h[c]);
   __syncwarp();
   float acc[AT][CPL];
+  {
+    float bv[CPL];
+    pk_lds_vec<CPL>(bias, lane, bv);
 #pragma unroll
-  for (int i = 0; i < CPL; ++i) {
-    const float bv = bias[lane + 32 * i];
+    for (int c = 0; c < AT; ++c)
 #pragma unroll
-    for (int c = 0; c < AT; ++c) acc[c][i] = bv;
+      for (int i = 0; i < CPL; ++i) acc[c][i] = bv[i];
   }
 #pragma unroll 2
   for (int k = 0; k < HP; k += 4) {
@@ -228,13 +272,11 @@ __device__ __forceinline__ void pk_hidden_layer(const float* __restrict__ WT, co
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
       float w[CPL];
-#pragma unroll
-      for (int i = 0; i < CPL; ++i) w[i] = WT[(k + kk) * HP + lane + 32 * i];
+      pk_lds_vec<CPL>(WT + (k + kk) * HP, lane, w);
 #pragma unroll
       for (int c = 0; c < AT; ++c) {
         const float x = kk == 0 ? hv[c].x : kk == 1 ? hv[c].y : kk == 2 ? hv[c].z : hv[c].w;
-#pragma unroll
-        for (int i = 0; i < CPL; ++i) acc[c][i] = fmaf(w[i], x, acc[c][i]);
+        pk_fma_vec<CPL>(acc[c], w, x);
       }
     }
   }
@@ -254,8 +296,7 @@ __device__ __forceinline__ void pk_mlp_tail(const float* s_tail, const PkLayout&
   for (int l = 1; l < lay.n_layers; ++l)
     pk_hidden_layer<CPL, AT>(s_tail + (lay.wl[l] - base), s_tail + (lay.b[l] - base), hbuf, h, lane);
   float wo[CPL];
-#pragma unroll
-  for (int i = 0; i < CPL; ++i) wo[i] = s_tail[lay.wout - base + lane + 32 * i];
+  pk_lds_vec<CPL>(s_tail + (lay.wout - base), lane, wo);
   const float bo = s_tail[lay.bout - base];
 #pragma unroll
   for (int c = 0; c < AT; ++c) {
@@ -281,135 +322,106 @@ __device__ __forceinline__ void pk_stage_weights(unsigned char* smem, const PkSm
   for (int i = threadIdx.x; i < nw; i += blockDim.x) dw[i] = __ldg(sw + i);
 }
 
+// ---- feature block of one battle, streamed from registers -------------------------------------------
+// g = start of the battle's (C, A) block (4-byte aligned only: C*A*4 is not a multiple of 16).
+// sv = the 50 state values in shared memory (padded with zeros to 64).
+__device__ __forceinline__ void pk_store_feature_block(float* __restrict__ g, int L, int A, const float* sv,
+                                                       const int* idx, int zero_row, int lane) {
+  const int m = (int)((reinterpret_cast<uintptr_t>(g) >> 2) & 3u);  // phase of the block inside a 16 B line
+  const int hc = (4 - m) & 3;                                       // floats before the first 16 B boundary
+  const int nchunks = (L - hc) >> 2;                                // whole 16 B chunks
+  const int ns = PK_N_STATE * A;                                    // state rows fill every column (:48)
+  float4* g4 = reinterpret_cast<float4*>(g + hc);
+  // chunks that overlap the state region carry values; everything behind is zeros until poked
+  const int n_state_chunks = min(nchunks, (ns - hc + 3) >> 2);
+  for (int j = lane; j < n_state_chunks; j += 32) {
+    const int e0 = hc + 4 * j;
+    int k = e0 / A, c = e0 - k * A;
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[i] = (e0 + i < ns) ? sv[k] : 0.0f;
+      if (++c == A) {
+        c = 0;
+        ++k;
+      }
+    }
+    g4[j] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int j = n_state_chunks + lane; j < nchunks; j += 32) g4[j] = z;
+  if (lane < hc) g[lane] = sv[lane / A];
+  {
+    const int e = hc + 4 * nchunks + lane;  // tail floats (item rows: zero unless poked below)
+    if (e < L) g[e] = e < ns ? sv[e / A] : 0.0f;
+  }
+  __syncwarp();  // orders the fill before the pokes of other lanes (same addresses)
+  // choice rows: ones in the first n_act columns only (feature_extractor.py:49)
+  for (int e = lane; e < 8 * PK_MAX_ACTIONS; e += 32) {
+    const int row = idx[e];
+    if (row != zero_row) g[row * A + (e >> 3)] = 1.0f;
+  }
+}
+
 template <int CPL, int AT>
 __global__ void __launch_bounds__(512, 1)
 pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __restrict__ prep, PkLayout lay,
                  float* __restrict__ feat, int* __restrict__ mask, float* __restrict__ q,
-                 int* __restrict__ action, PkSelect sel, int n_writers, int nbuf) {
+                 int* __restrict__ action, PkSelect sel) {
   constexpr int HP = 32 * CPL;
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  const int n_mlp = nwarps - n_writers;
-  const bool with_mlp = prep != nullptr && n_mlp > 0;
+  const bool with_mlp = prep != nullptr;
   const int L = lay.C * A;  // floats per battle
-  const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
+  const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp);
 
-  // ---- prologue ---------------------------------------------------------------------------------
-  if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
-  if (feat != nullptr) {
-    float4* z = reinterpret_cast<float4*>(smem + plan.staging);
-    const int nz = (int)((plan.lbuf * n_writers * nbuf) >> 2);
-    for (int i = threadIdx.x; i < nz; i += blockDim.x) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (with_mlp) {
+    pk_stage_weights(smem, plan, prep, lay);
+    __syncthreads();
   }
-  __syncthreads();
 
   unsigned char* wa = smem + plan.warp_area + warp * plan.warp_stride;
-
-  if (warp < n_writers) {
-    // =========================== writer warp ====================================================
-    if (feat == nullptr && (mask == nullptr || with_mlp)) return;
-    uint4* recs = reinterpret_cast<uint4*>(wa);
-    float* stg = reinterpret_cast<float*>(smem + plan.staging) + (size_t)warp * nbuf * plan.lbuf;
-    const long long reuse_stride = (long long)nbuf * n_writers * gridDim.x;
-    int use = 0;
-    for (int n = warp;; n += n_writers, ++use) {
-      const long long b = blockIdx.x + (long long)n * gridDim.x;
-      if (b >= B) break;
-      const int slot = use % nbuf;
-      float* tile = stg + (size_t)slot * plan.lbuf;
-      uint4* rec = recs + slot * 9;
-      const uint8_t* r = reinterpret_cast<const uint8_t*>(rec);
-      if (feat != nullptr && use >= nbuf) {
-        // the bulk store that last used this tile must have finished READING it
-        if (lane == 0) {
-          switch (nbuf) {
-            case 1: pk_bulk_wait_read<0>(); break;
-            case 2: pk_bulk_wait_read<1>(); break;
-            case 3: pk_bulk_wait_read<2>(); break;
-            default: pk_bulk_wait_read<3>(); break;
-          }
-        }
-        __syncwarp();
-        const int m_old = (int)(((unsigned long long)(b - reuse_stride) * (unsigned long long)L) & 3ull);
-        const int n_old = min((int)r[PK_OFF_NACT], A);
-        pk_poke_choice(tile + m_old, r, A, n_old, lane, 0.0f);  // un-poke: the tile is zeros again (bar state rows)
-        __syncwarp();
-      }
-      if (lane < 9) rec[lane] = __ldg(packed + b * 9 + lane);
-      __syncwarp();
-      const int n_act = min((int)r[PK_OFF_NACT], A);
-      if (mask != nullptr && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;  // feature_extractor.py:50-51
-      if (feat != nullptr) {
-        const int m = (int)(((unsigned long long)b * (unsigned long long)L) & 3ull);  // global 16 B phase of this block
-        const int ns = PK_N_STATE * A;
-        // a previous use of this tile with a different phase leaves <= 3 stale state values at either edge
-        if (lane < 3) {
-          if (lane < m) tile[lane] = 0.0f;
-          if (m + lane < 3) tile[ns + m + lane] = 0.0f;
-        }
-        __syncwarp();
-        // state rows fill every column, legal or not (feature_extractor.py:48)
-        const float s0 = pk_state_feature(r, lane);
-        const float s1 = pk_state_feature(r, lane + 32);
-        for (int c = 0; c < A; ++c) tile[m + lane * A + c] = s0;
-        if (lane + 32 < PK_N_STATE)
-          for (int c = 0; c < A; ++c) tile[m + (lane + 32) * A + c] = s1;
-        // choice rows only in the first n_act columns (feature_extractor.py:49)
-        pk_poke_choice(tile + m, r, A, n_act, lane, 1.0f);
-        pk_fence_proxy_async_smem();
-        __syncwarp();
-        const int hc = (4 - m) & 3;          // floats before the first 16 B boundary
-        const int body = (L - hc) & ~3;      // floats moved by the TMA engine
-        const int tc = L - hc - body;        // floats after the last 16 B boundary
-        float* g = feat + (size_t)b * L;
-        if (lane == 0) {
-          pk_bulk_store(g + hc, tile + m + hc, (uint32_t)body * 4u);
-          pk_bulk_commit();
-        }
-        if (lane < hc) g[lane] = tile[m + lane];
-        if (lane >= 8 && lane < 8 + tc) {
-          const int i = hc + body + (lane - 8);
-          g[i] = tile[m + i];
-        }
-      }
-    }
-    if (feat != nullptr && lane == 0) pk_bulk_wait_all();
-    return;
-  }
-
-  // =============================== MLP warp =======================================================
-  if (!with_mlp) return;
-  const bool mask_here = mask != nullptr && feat == nullptr;  // otherwise the writer warps emit it
-  const int mw = warp - n_writers;
   uint4* rec = reinterpret_cast<uint4*>(wa);
   const uint8_t* r = reinterpret_cast<const uint8_t*>(rec);
   float* sv = reinterpret_cast<float*>(wa + PK_WARP_REC_BYTES);
   int* idx = reinterpret_cast<int*>(wa + PK_WARP_REC_BYTES + PK_WARP_SV_BYTES);
-  float* hbuf = reinterpret_cast<float*>(wa + PK_WARP_REC_BYTES + PK_WARP_SV_BYTES + PK_WARP_IDX_BYTES);
+  float* hbuf = reinterpret_cast<float*>(wa + PK_WARP_FIXED_BYTES);
   const float* s_tail = reinterpret_cast<const float*>(smem + plan.tail);
   const float* s_w1s = reinterpret_cast<const float*>(smem + plan.w1s);
   const float* w1t = prep + lay.w1t;
   const int zero_row = lay.C;
   float b1r[CPL];
-#pragma unroll
-  for (int i = 0; i < CPL; ++i) b1r[i] = s_tail[lane + 32 * i];  // lay.b[0] is the start of the tail
+  if (with_mlp) pk_lds_vec<CPL>(s_tail, lane, b1r);  // lay.b[0] is the start of the tail
 
-  for (int n = mw;; n += n_mlp) {
-    const long long b = blockIdx.x + (long long)n * gridDim.x;
-    if (b >= B) break;
-    __syncwarp();
-    if (lane < 9) rec[lane] = __ldg(packed + b * 9 + lane);
+  // battles are dealt round-robin over every warp of the grid
+  const long long stride = (long long)gridDim.x * nwarps;
+  long long b = (long long)warp * gridDim.x + blockIdx.x;
+  uint4 cur = make_uint4(0u, 0u, 0u, 0u);
+  if (b < B && lane < 9) cur = __ldg(packed + b * 9 + lane);
+
+  for (; b < B; b += stride) {
+    __syncwarp();  // the previous battle's readers of rec / sv / idx are done
+    if (lane < 9) rec[lane] = cur;
+    if (b + stride < B && lane < 9) cur = __ldg(packed + (b + stride) * 9 + lane);  // prefetch, consumed next turn
     __syncwarp();
     const int n_act = min((int)r[PK_OFF_NACT], A);
-    if (mask_here && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;
+    if (mask != nullptr && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;  // feature_extractor.py:50-51
     sv[lane] = pk_state_feature(r, lane);
     sv[lane + 32] = pk_state_feature(r, lane + 32);
-    for (int e = lane; e < 8 * AT; e += 32) {
-      const int c = e >> 3, t = e & 7;
-      int row = c < n_act ? pk_choice_row(r, c, t) : -1;
-      idx[e] = row < 0 ? zero_row : row;
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int e = lane + 32 * it;
+      if (e < 8 * PK_MAX_ACTIONS) {
+        const int c = e >> 3;
+        const int row = c < n_act ? pk_choice_row(r, c, e & 7) : -1;
+        idx[e] = row < 0 ? zero_row : row;
+      }
     }
     __syncwarp();
+
+    if (feat != nullptr) pk_store_feature_block(feat + (size_t)b * L, L, A, sv, idx, zero_row, lane);
+    if (!with_mlp) continue;
 
     // ---- layer 0, state part: shared by every column of this battle ------------------------------
     float base[CPL];
@@ -422,8 +434,9 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __
       for (int kk = 0; kk < 4; ++kk) {
         const float x = kk == 0 ? s4.x : kk == 1 ? s4.y : kk == 2 ? s4.z : s4.w;
         if (x != 0.0f) {  // warp-uniform; k >= 50 reads zeros
-#pragma unroll
-          for (int i = 0; i < CPL; ++i) base[i] = fmaf(s_w1s[(k4 + kk) * HP + lane + 32 * i], x, base[i]);
+          float w[CPL];
+          pk_lds_vec<CPL>(s_w1s + (k4 + kk) * HP, lane, w);
+          pk_fma_vec<CPL>(base, w, x);
         }
       }
     }
@@ -437,24 +450,18 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __
         const int4 ia = *reinterpret_cast<const int4*>(idx + 8 * c);
         const int4 ib = *reinterpret_cast<const int4*>(idx + 8 * c + 4);
         float g0[CPL], g1[CPL], g2[CPL];
-#pragma unroll
-        for (int i = 0; i < CPL; ++i) {
-          g0[i] = __ldg(w1t + (size_t)ia.z * HP + lane + 32 * i);  // species
-          g1[i] = __ldg(w1t + (size_t)ia.w * HP + lane + 32 * i);  // item
-          g2[i] = __ldg(w1t + (size_t)ib.x * HP + lane + 32 * i);  // first move
-        }
-        const uint8_t* a = r + PK_OFF_ACT + 12 * c;
-        const bool more = a[0] != 0 || a[3] > 1;  // switch / force flags or a move list (switch target)
+        pk_ldg_vec<CPL>(w1t + (size_t)ia.z * HP, lane, g0);  // species
+        pk_ldg_vec<CPL>(w1t + (size_t)ia.w * HP, lane, g1);  // item
+        pk_ldg_vec<CPL>(w1t + (size_t)ib.x * HP, lane, g2);  // first move
+        // any of: switch / force flags, further moves (a switch target's move list)
+        const bool more = min(min(ia.x, ia.y), min(ib.y, min(ib.z, ib.w))) != zero_row;  // valid rows are < zero_row
         if (more) {
           float g3[CPL], g4[CPL], g5[CPL], g6[CPL], g7[CPL];
-#pragma unroll
-          for (int i = 0; i < CPL; ++i) {
-            g3[i] = __ldg(w1t + (size_t)ia.x * HP + lane + 32 * i);
-            g4[i] = __ldg(w1t + (size_t)ia.y * HP + lane + 32 * i);
-            g5[i] = __ldg(w1t + (size_t)ib.y * HP + lane + 32 * i);
-            g6[i] = __ldg(w1t + (size_t)ib.z * HP + lane + 32 * i);
-            g7[i] = __ldg(w1t + (size_t)ib.w * HP + lane + 32 * i);
-          }
+          pk_ldg_vec<CPL>(w1t + (size_t)ia.x * HP, lane, g3);
+          pk_ldg_vec<CPL>(w1t + (size_t)ia.y * HP, lane, g4);
+          pk_ldg_vec<CPL>(w1t + (size_t)ib.y * HP, lane, g5);
+          pk_ldg_vec<CPL>(w1t + (size_t)ib.z * HP, lane, g6);
+          pk_ldg_vec<CPL>(w1t + (size_t)ib.w * HP, lane, g7);
 #pragma unroll
           for (int i = 0; i < CPL; ++i) h[c][i] = ((((h[c][i] + g3[i]) + g4[i]) + g5[i]) + g6[i]) + g7[i];
         }
@@ -524,8 +531,7 @@ pk_dense_forward_kernel(const float* __restrict__ feat, int B, int A, const floa
   float* xt = hbuf + AT * HP;
   const float* w1t = prep + lay.w1t;
   float b1r[CPL];
-#pragma unroll
-  for (int i = 0; i < CPL; ++i) b1r[i] = s_tail[lane + 32 * i];
+  pk_lds_vec<CPL>(s_tail, lane, b1r);
 
   for (long long b = (long long)blockIdx.x * nwarps + warp; b < B; b += (long long)gridDim.x * nwarps) {
     const float* g = feat + (size_t)b * L;
@@ -548,15 +554,10 @@ pk_dense_forward_kernel(const float* __restrict__ feat, int B, int A, const floa
         const int kk = k0 + __ffs(rows) - 1;
         rows &= rows - 1u;
         float w[CPL];
-#pragma unroll
-        for (int i = 0; i < CPL; ++i) w[i] = __ldg(w1t + (size_t)kk * HP + lane + 32 * i);
+        pk_ldg_vec<CPL>(w1t + (size_t)kk * HP, lane, w);
 #pragma unroll
         for (int c = 0; c < AT; ++c) {
-          if (c < A) {
-            const float x = xt[kk * A + c];
-#pragma unroll
-            for (int i = 0; i < CPL; ++i) h[c][i] = fmaf(w[i], x, h[c][i]);
-          }
+          if (c < A) pk_fma_vec<CPL>(h[c], w, xt[kk * A + c]);
         }
       }
     }

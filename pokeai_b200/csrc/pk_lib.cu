@@ -39,11 +39,9 @@ struct PkGlobal {
   int sm_count = 0;
   int max_smem = 0;
   PkDeviceTables tab;
-  // tuning knobs of pk_decide (environment: PK_DECIDE_WARPS / PK_DECIDE_WRITERS / PK_DECIDE_NBUF / PK_ENCODE_WARPS)
-  int decide_warps = 12;
-  int decide_writers = 2;
-  int decide_nbuf = 2;
-  int encode_warps = 4;
+  // tuning knobs (environment: PK_DECIDE_WARPS / PK_ENCODE_WARPS / PK_CTAS_PER_SM)
+  int decide_warps = 16;
+  int encode_warps = 16;
   int ctas_per_sm = 1;
 };
 static PkGlobal g;
@@ -83,10 +81,9 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.device = device;
   g.sm_count = prop.multiProcessorCount;
   g.max_smem = (int)prop.sharedMemPerBlockOptin;
-  g.decide_warps = env_int("PK_DECIDE_WARPS", 12, 2, 16);
-  g.decide_writers = env_int("PK_DECIDE_WRITERS", 2, 1, 8);
-  g.decide_nbuf = env_int("PK_DECIDE_NBUF", 2, 1, PK_MAX_NBUF);
-  g.encode_warps = env_int("PK_ENCODE_WARPS", 4, 1, 8);
+  g.decide_warps = env_int("PK_DECIDE_WARPS", 16, 1, 16);
+  g.encode_warps = env_int("PK_ENCODE_WARPS", 16, 1, 16);
+  g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
   return PK_OK;
 }
 
@@ -168,7 +165,7 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   PK_REQUIRE(A >= 1 && A <= PK_MAX_ACTIONS, "A=%d not in 1..%d", A, PK_MAX_ACTIONS);
   if (B == 0) return PK_OK;
   PK_REQUIRE(packed != nullptr && aligned16(packed), "packed observations must be non-null and 16-byte aligned");
-  PK_REQUIRE(feat == nullptr || aligned16(feat), "feature buffer must be 16-byte aligned");
+  PK_REQUIRE(feat == nullptr || (reinterpret_cast<uintptr_t>(feat) & 3u) == 0, "feature buffer must be 4-byte aligned");
   const bool with_mlp = prepared != nullptr;
   PkLayout lay;
   PkSelect ps;
@@ -199,38 +196,25 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   }
   const int CPL = lay.HP / 32;
   const int AT = pk_at_for(A);
-  int nwarps, n_writers, nbuf;
-  if (with_mlp) {
-    nwarps = g.decide_warps;
-    n_writers = feat != nullptr ? g.decide_writers : 0;
-    nbuf = feat != nullptr ? g.decide_nbuf : 1;
-    if (n_writers >= nwarps) n_writers = nwarps - 1;
-  } else {
-    nwarps = n_writers = g.encode_warps;
-    nbuf = feat != nullptr ? g.decide_nbuf : 1;
-  }
-  PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
-  while (plan.total > (unsigned)g.max_smem && nwarps > n_writers + 1) {  // drop MLP warps until the plan fits
+  int nwarps = with_mlp ? g.decide_warps : g.encode_warps;
+  PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp);
+  while (plan.total > (unsigned)g.max_smem && nwarps > 1) {  // drop warps until the plan fits
     --nwarps;
-    plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
-  }
-  while (plan.total > (unsigned)g.max_smem && (nbuf > 1 || n_writers > 1)) {
-    if (nbuf > 1) --nbuf;
-    else { --n_writers; if (!with_mlp) nwarps = n_writers; }
-    plan = pk_smem_plan(lay, AT, nwarps, n_writers, nbuf, A, with_mlp);
+    plan = pk_smem_plan(lay, AT, nwarps, with_mlp);
   }
   if (plan.total > (unsigned)g.max_smem)
     return pk_fail(PK_ERR_UNSUPPORTED,
                    "network %d x %d does not fit the fused small-net kernel (%u B shared memory needed, %d available)",
                    n_layers, n_channels, plan.total, g.max_smem);
-  const int grid = B < g.sm_count ? B : g.sm_count;
+  int grid = (B + nwarps - 1) / nwarps;
+  if (grid > g.sm_count * g.ctas_per_sm) grid = g.sm_count * g.ctas_per_sm;
   const uint4* pk = reinterpret_cast<const uint4*>(packed);
 #define PK_LAUNCH_DECIDE(C_, A_)                                                                              \
   {                                                                                                           \
     int rc_ = pk_set_smem(pk_decide_kernel<C_, A_>, plan.total);                                              \
     if (rc_) return rc_;                                                                                      \
     pk_decide_kernel<C_, A_><<<grid, nwarps * 32, plan.total, st>>>(pk, B, A, prepared, lay, feat, mask, q,   \
-                                                                    action, ps, n_writers, nbuf);             \
+                                                                    action, ps);                              \
   }
   PK_DISPATCH_CPL_AT(CPL, AT, PK_LAUNCH_DECIDE);
 #undef PK_LAUNCH_DECIDE
