@@ -230,10 +230,13 @@ struct PkSmemPlan {
   unsigned w1s;          // first PK_N_STATE rows of W1^T
   unsigned warp_area;    // per-warp scratch
   unsigned warp_stride;
+  unsigned zero_tile;    // block-wide tile of zeros: source of the TMA zero fill
+  unsigned zero_bytes;
   unsigned total;
 };
 
-__host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, int nwarps, bool with_mlp) {
+__host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, int nwarps, bool with_mlp,
+                                                   bool zero_tile) {
   PkSmemPlan p;
   unsigned o = 0;
   p.tail = o;
@@ -243,6 +246,10 @@ __host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, 
   p.warp_area = o;
   p.warp_stride = PK_WARP_FIXED_BYTES + (with_mlp ? (unsigned)AT * lay.HP * 4u : 0u);
   o += p.warp_stride * nwarps;
+  o = (o + 127u) & ~127u;
+  p.zero_tile = o;
+  p.zero_bytes = zero_tile ? ((((unsigned)lay.C * AT * 4u) + 15u) & ~15u) : 0u;
+  o += p.zero_bytes;
   p.total = o;
   return p;
 }
@@ -322,64 +329,83 @@ __device__ __forceinline__ void pk_stage_weights(unsigned char* smem, const PkSm
   for (int i = threadIdx.x; i < nw; i += blockDim.x) dw[i] = __ldg(sw + i);
 }
 
-// ---- feature block of one battle, streamed from registers -------------------------------------------
+// ---- feature block of one battle ---------------------------------------------------------------------
 // g = start of the battle's (C, A) block (4-byte aligned only: C*A*4 is not a multiple of 16).
 // sv = the 50 state values in shared memory (padded with zeros to 64).
-__device__ __forceinline__ void pk_store_feature_block(float* __restrict__ g, int L, int A, const float* sv,
-                                                       const int* idx, int zero_row, int lane) {
+// The ~450 state values go out as coalesced 16-byte stores from registers.  The zeros behind them
+// (about 20 KB) are either stored the same way (zero_tile == nullptr) or handed to the TMA engine as one
+// bulk store from a block-wide tile of zeros in shared memory; the caller pokes the ones afterwards
+// (pk_poke_feature_block), for the TMA variant only after cp.async.bulk.wait_group has returned.
+template <int A>
+__device__ __forceinline__ void pk_store_feature_block(float* __restrict__ g, int L, const float* sv,
+                                                       const float* zero_tile, int lane) {
   const int m = (int)((reinterpret_cast<uintptr_t>(g) >> 2) & 3u);  // phase of the block inside a 16 B line
   const int hc = (4 - m) & 3;                                       // floats before the first 16 B boundary
   const int nchunks = (L - hc) >> 2;                                // whole 16 B chunks
-  const int ns = PK_N_STATE * A;                                    // state rows fill every column (:48)
+  constexpr int ns = PK_N_STATE * A;                                // state rows fill every column (:48)
   float4* g4 = reinterpret_cast<float4*>(g + hc);
   // chunks that overlap the state region carry values; everything behind is zeros until poked
   const int n_state_chunks = min(nchunks, (ns - hc + 3) >> 2);
+  if (zero_tile != nullptr && lane == 0 && nchunks > n_state_chunks) {
+    pk_bulk_store(g4 + n_state_chunks, zero_tile, (uint32_t)(nchunks - n_state_chunks) * 16u);
+    pk_bulk_commit();
+  }
   for (int j = lane; j < n_state_chunks; j += 32) {
     const int e0 = hc + 4 * j;
-    int k = e0 / A, c = e0 - k * A;
     float v[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      v[i] = (e0 + i < ns) ? sv[k] : 0.0f;
-      if (++c == A) {
-        c = 0;
-        ++k;
-      }
-    }
+    for (int i = 0; i < 4; ++i) v[i] = (e0 + i < ns) ? sv[(e0 + i) / A] : 0.0f;
     g4[j] = make_float4(v[0], v[1], v[2], v[3]);
   }
-  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (zero_tile == nullptr) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 4
-  for (int j = n_state_chunks + lane; j < nchunks; j += 32) g4[j] = z;
+    for (int j = n_state_chunks + lane; j < nchunks; j += 32) g4[j] = z;
+  }
   if (lane < hc) g[lane] = sv[lane / A];
   {
-    const int e = hc + 4 * nchunks + lane;  // tail floats (item rows: zero unless poked below)
+    const int e = hc + 4 * nchunks + lane;  // tail floats (item rows: zero unless poked)
     if (e < L) g[e] = e < ns ? sv[e / A] : 0.0f;
-  }
-  __syncwarp();  // orders the fill before the pokes of other lanes (same addresses)
-  // choice rows: ones in the first n_act columns only (feature_extractor.py:49)
-  for (int e = lane; e < 8 * PK_MAX_ACTIONS; e += 32) {
-    const int row = idx[e];
-    if (row != zero_row) g[row * A + (e >> 3)] = 1.0f;
   }
 }
 
-template <int CPL, int AT>
+// choice rows: ones in the first n_act columns only (feature_extractor.py:49).  Must run after the fill
+// of the same addresses is ordered before it (__syncwarp for the register stores, wait_group for TMA).
+template <int A>
+__device__ __forceinline__ void pk_poke_feature_block(float* __restrict__ g, const int* idx, int zero_row, int lane) {
+#pragma unroll
+  for (int it = 0; it < 3; ++it) {
+    const int e = lane + 32 * it;
+    if (e < 8 * A) {
+      const int row = idx[e];
+      if (row != zero_row) g[row * A + (e >> 3)] = 1.0f;
+    }
+  }
+}
+
+template <int CPL, int A>
 __global__ void __launch_bounds__(512, 1)
-pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __restrict__ prep, PkLayout lay,
+pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restrict__ prep, PkLayout lay,
                  float* __restrict__ feat, int* __restrict__ mask, float* __restrict__ q,
-                 int* __restrict__ action, PkSelect sel) {
+                 int* __restrict__ action, PkSelect sel, int zero_by_tma) {
   constexpr int HP = 32 * CPL;
+  constexpr int AT = A;
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const bool with_mlp = prep != nullptr;
   const int L = lay.C * A;  // floats per battle
-  const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp);
+  const bool use_tma = feat != nullptr && zero_by_tma != 0;
+  const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp, use_tma);
 
-  if (with_mlp) {
-    pk_stage_weights(smem, plan, prep, lay);
-    __syncthreads();
+  if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
+  const float* zero_tile = nullptr;
+  if (use_tma) {
+    float4* z = reinterpret_cast<float4*>(smem + plan.zero_tile);
+    for (int i = threadIdx.x; i < (int)(plan.zero_bytes >> 4); i += blockDim.x) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    pk_fence_proxy_async_smem();  // the async proxy (TMA) reads what the generic proxy just wrote
+    zero_tile = reinterpret_cast<const float*>(z);
   }
+  if (with_mlp || use_tma) __syncthreads();
 
   unsigned char* wa = smem + plan.warp_area + warp * plan.warp_stride;
   uint4* rec = reinterpret_cast<uint4*>(wa);
@@ -412,7 +438,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
       const int e = lane + 32 * it;
-      if (e < 8 * PK_MAX_ACTIONS) {
+      if (e < 8 * A) {
         const int c = e >> 3;
         const int row = c < n_act ? pk_choice_row(r, c, e & 7) : -1;
         idx[e] = row < 0 ? zero_row : row;
@@ -420,7 +446,18 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __
     }
     __syncwarp();
 
-    if (feat != nullptr) pk_store_feature_block(feat + (size_t)b * L, L, A, sv, idx, zero_row, lane);
+    float* gfeat = feat != nullptr ? feat + (size_t)b * L : nullptr;
+    if (gfeat != nullptr) {
+      pk_store_feature_block<A>(gfeat, L, sv, zero_tile, lane);
+      if (!use_tma) {
+        __syncwarp();  // orders the fill before the pokes of other lanes (same addresses)
+        pk_poke_feature_block<A>(gfeat, idx, zero_row, lane);
+      } else if (!with_mlp) {
+        if (lane == 0) pk_bulk_wait_all();
+        __syncwarp();
+        pk_poke_feature_block<A>(gfeat, idx, zero_row, lane);
+      }
+    }
     if (!with_mlp) continue;
 
     // ---- layer 0, state part: shared by every column of this battle ------------------------------
@@ -482,6 +519,11 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, int A, const float* __
     if (action != nullptr) {
       const int act = pk_select_dev<AT>(qv, (1u << n_act) - 1u, A, sel, b, lane == 0);
       if (lane == 0) action[b] = act;
+    }
+    if (gfeat != nullptr && use_tma) {  // the zeros have landed by now; finish the block
+      if (lane == 0) pk_bulk_wait_all();
+      __syncwarp();
+      pk_poke_feature_block<A>(gfeat, idx, zero_row, lane);
     }
   }
 }

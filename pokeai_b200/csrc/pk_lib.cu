@@ -39,10 +39,11 @@ struct PkGlobal {
   int sm_count = 0;
   int max_smem = 0;
   PkDeviceTables tab;
-  // tuning knobs (environment: PK_DECIDE_WARPS / PK_ENCODE_WARPS / PK_CTAS_PER_SM)
+  // tuning knobs (environment: PK_DECIDE_WARPS / PK_ENCODE_WARPS / PK_CTAS_PER_SM / PK_ZERO_TMA)
   int decide_warps = 16;
   int encode_warps = 16;
   int ctas_per_sm = 1;
+  int zero_by_tma = 1;
 };
 static PkGlobal g;
 
@@ -84,6 +85,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.decide_warps = env_int("PK_DECIDE_WARPS", 16, 1, 16);
   g.encode_warps = env_int("PK_ENCODE_WARPS", 16, 1, 16);
   g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
+  g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
   return PK_OK;
 }
 
@@ -195,12 +197,12 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
     lay = pk_make_layout(1, 32, g.tab.C);
   }
   const int CPL = lay.HP / 32;
-  const int AT = pk_at_for(A);
+  const bool use_tma = feat != nullptr && g.zero_by_tma != 0;
   int nwarps = with_mlp ? g.decide_warps : g.encode_warps;
-  PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp);
+  PkSmemPlan plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma);
   while (plan.total > (unsigned)g.max_smem && nwarps > 1) {  // drop warps until the plan fits
     --nwarps;
-    plan = pk_smem_plan(lay, AT, nwarps, with_mlp);
+    plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma);
   }
   if (plan.total > (unsigned)g.max_smem)
     return pk_fail(PK_ERR_UNSUPPORTED,
@@ -213,10 +215,26 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   {                                                                                                           \
     int rc_ = pk_set_smem(pk_decide_kernel<C_, A_>, plan.total);                                              \
     if (rc_) return rc_;                                                                                      \
-    pk_decide_kernel<C_, A_><<<grid, nwarps * 32, plan.total, st>>>(pk, B, A, prepared, lay, feat, mask, q,   \
-                                                                    action, ps);                              \
+    pk_decide_kernel<C_, A_><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask, q,      \
+                                                                    action, ps, use_tma ? 1 : 0);             \
   }
-  PK_DISPATCH_CPL_AT(CPL, AT, PK_LAUNCH_DECIDE);
+#define PK_LAUNCH_DECIDE_A(C_)                                        \
+  switch (A) {                                                        \
+    case 1: PK_LAUNCH_DECIDE(C_, 1) break;                            \
+    case 2: PK_LAUNCH_DECIDE(C_, 2) break;                            \
+    case 3: PK_LAUNCH_DECIDE(C_, 3) break;                            \
+    case 4: PK_LAUNCH_DECIDE(C_, 4) break;                            \
+    case 5: PK_LAUNCH_DECIDE(C_, 5) break;                            \
+    case 6: PK_LAUNCH_DECIDE(C_, 6) break;                            \
+    case 7: PK_LAUNCH_DECIDE(C_, 7) break;                            \
+    case 8: PK_LAUNCH_DECIDE(C_, 8) break;                            \
+    default: PK_LAUNCH_DECIDE(C_, 9) break;                           \
+  }
+  if (CPL == 1) { PK_LAUNCH_DECIDE_A(1) }
+  else if (CPL == 2) { PK_LAUNCH_DECIDE_A(2) }
+  else if (CPL == 4) { PK_LAUNCH_DECIDE_A(4) }
+  else return pk_fail(PK_ERR_UNSUPPORTED, "the fused small-net kernel supports up to 128 channels (got %d)", n_channels);
+#undef PK_LAUNCH_DECIDE_A
 #undef PK_LAUNCH_DECIDE
   PK_CUDA(cudaGetLastError());
   return PK_OK;

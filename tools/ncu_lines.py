@@ -8,6 +8,7 @@ import sys
 rep = sys.argv[1]
 which = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 25
+SORT = sys.argv[4] if len(sys.argv) > 4 else "samples"
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
@@ -56,7 +57,7 @@ print("kernel:", wanted)
 tot_s = sum(e["samples"] for e in lines.values()) or 1
 tot_i = sum(e["inst"] for e in lines.values()) or 1
 print(f"total samples {tot_s}  total warp-instructions {tot_i}")
-for (f, ln), e in sorted(lines.items(), key=lambda kv: -kv[1]["samples"])[:top]:
+for (f, ln), e in sorted(lines.items(), key=lambda kv: -kv[1][SORT])[:top]:
     st = sorted(e["stalls"].items(), key=lambda kv: -kv[1])[:3]
     st = " ".join(f"{k[6:]}={v}" for k, v in st if v)
     print(f"{f}:{ln:4d} samp {100*e['samples']/tot_s:5.1f}% inst {100*e['inst']/tot_i:5.1f}% | {st:45s} | {e['src']}")
