@@ -208,9 +208,17 @@ PK_API int pk_session_create(pk_session** out, int max_batch, int A, int materia
 PK_API void pk_session_destroy(pk_session* s);
 /* weights given as HOST pointers in state_dict layout */
 PK_API int pk_session_load_weights(pk_session* s, const pk_mlp* host_mlp);
+/* use caller-owned prepared weights on the device instead (no copy; must outlive the calls) */
+PK_API int pk_session_use_prepared(pk_session* s, const float* prepared_dev, int n_layers, int n_channels);
 PK_API int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
                            float temperature, const float* u_explore_host, const float* u_pick_host,
                            float* q_host, int32_t* action_host);
+/* packed_host[B] -> feat_host (B, C, A), mask_host (B, A): host-buffer FeatureExtractor.transform
+ * (feature_extractor.py:40-52).  Needs a session created with materialise_features != 0. */
+PK_API int pk_session_encode_host(pk_session* s, const pk_obs* packed_host, int B, float* feat_host,
+                           int32_t* mask_host);
+/* copy the features / masks the last pk_session_decide_host materialised back to the host */
+PK_API int pk_session_fetch(pk_session* s, int B, float* feat_host, int32_t* mask_host);
 /* device pointers of the session's last results (valid until the next call) */
 PK_API const float* pk_session_features(const pk_session* s);
 PK_API const int32_t* pk_session_mask(const pk_session* s);

@@ -69,7 +69,10 @@ _SIGNATURES = {
     "pk_session_create": (C.c_int, [C.POINTER(_vp), _i, _i, _i]),
     "pk_session_destroy": (None, [_vp]),
     "pk_session_load_weights": (C.c_int, [_vp, C.POINTER(pk_mlp)]),
+    "pk_session_use_prepared": (C.c_int, [_vp, _vp, _i, _i]),
     "pk_session_decide_host": (C.c_int, [_vp, _vp, _i, _i, _f, _f, _vp, _vp, _vp, _vp]),
+    "pk_session_encode_host": (C.c_int, [_vp, _vp, _i, _vp, _vp]),
+    "pk_session_fetch": (C.c_int, [_vp, _i, _vp, _vp]),
     "pk_session_features": (_vp, [_vp]),
     "pk_session_mask": (_vp, [_vp]),
 }

@@ -1,0 +1,146 @@
+"""Agent / AgentVal / AgentTrain with the reference's interface
+(pokeai/ai/generic_move_model/agent.py:13-45, agent_val.py:4-14, agent_train.py:9-44),
+running on the fused B200 decision kernel.
+
+``act(obs, reward) -> int`` is the call RLPolicy makes (rl_policy.py:95-105); ``act_batch`` is
+the same decision for many battles in one launch.  The host side only packs the observation
+into the pinned 144-byte record; encode, MLP and the masked choice happen in one kernel.
+"""
+from __future__ import annotations
+
+import json
+import logging
+from logging import getLogger
+from typing import Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .feature_extractor import FeatureExtractor
+from .replay_buffer import ReplayBuffer, ReplayBufferItem
+
+logger = getLogger(__name__)
+
+
+class Agent:
+    def __init__(self, model: torch.nn.Module, feature_extractor: FeatureExtractor):
+        self._model = model
+        self._feature_extractor = feature_extractor
+
+    def act(self, obs: object, reward: float) -> int:
+        raise NotImplementedError
+
+    def stop_episode(self, reward: float) -> None:
+        raise NotImplementedError
+
+    # -- device plumbing ---------------------------------------------------------------------------
+    def _session(self, n: int):
+        s = self._feature_extractor.session(n)
+        m = self._model
+        s.use_prepared(m.prepared(s.device), m.n_layers, m.n_channels) if hasattr(m, "prepared") else s.load_model(m)
+        return s
+
+    # -- dense-input Q (agent.py:23-30; used by party_evaluator.py:102, party_evaluator_quick.py:101) ---
+    def _calc_q_vector(self, obs_vector) -> np.ndarray:
+        return self._calc_q_vector_batch(obs_vector[np.newaxis, ...])[0]
+
+    def _calc_q_vector_batch(self, obs_vector_batch) -> np.ndarray:
+        s = self._feature_extractor.session(1)
+        x = torch.from_numpy(np.ascontiguousarray(obs_vector_batch, dtype=np.float32)).to(s.device)
+        q = self._model(x)
+        return q.cpu().numpy()
+
+    def _act_by_model(self, obs_vector, action_mask) -> int:
+        q_vector = self._calc_q_vector(obs_vector)
+        q_vector[action_mask == 0] = -np.inf
+        action = int(np.argmax(q_vector))
+        if logger.isEnabledFor(logging.DEBUG):
+            logger.debug("q_func: " + json.dumps({"q_func": q_vector.tolist(), "action": action}))
+        return action
+
+    def _act_random(self, obs_vector, action_mask) -> int:
+        actions = np.flatnonzero(action_mask)
+        return int(np.random.choice(actions))
+
+    # -- fused path -----------------------------------------------------------------------------------
+    def q_and_action_batch(self, obs_list, mode: int = N.PK_SELECT_ARGMAX, eps: float = 0.0,
+                           temperature: float = 1.0, u_explore: Optional[np.ndarray] = None,
+                           u_pick: Optional[np.ndarray] = None):
+        """Observations (objects or packed records) -> (q (B, A) float32 with -inf NOT applied,
+        action (B,) int32).  Views of pinned buffers, valid until the next call."""
+        n = len(obs_list)
+        s = self._session(n)
+        self._feature_extractor.pack(obs_list, out=s.packed)
+        if mode == N.PK_SELECT_EPSGREEDY:
+            s.u_explore[:n] = u_explore
+        if mode != N.PK_SELECT_ARGMAX:
+            s.u_pick[:n] = u_pick
+        return s.decide(n, mode, eps, temperature)
+
+    def act_batch(self, obs_list) -> np.ndarray:
+        """Greedy decisions for a batch: q[mask == 0] = -inf; argmax (agent.py:32-35)."""
+        return self.q_and_action_batch(obs_list)[1].copy()
+
+    def _log_q(self, q: np.ndarray, n_act: int, action: int) -> None:
+        if logger.isEnabledFor(logging.DEBUG):
+            qq = q.astype(np.float32).copy()
+            qq[n_act:] = -np.inf
+            logger.debug("q_func: " + json.dumps({"q_func": qq.tolist(), "action": action}))
+
+
+class AgentVal(Agent):
+    def __init__(self, model, feature_extractor):
+        super().__init__(model, feature_extractor)
+
+    def act(self, obs: object, reward: float) -> int:
+        q, a = self.q_and_action_batch([obs])
+        action = int(a[0])
+        self._log_q(q[0], len(obs.possible_actions), action)
+        return action
+
+    def stop_episode(self, reward: float) -> None:
+        pass
+
+
+class AgentTrain(Agent):
+    def __init__(self, model, feature_extractor: FeatureExtractor, epsilon: float):
+        super().__init__(model, feature_extractor)
+        self._replay_buffer = ReplayBuffer(None)
+        self._epsilon = epsilon
+        self._last_state = None
+        self._last_action_mask = None
+        self._last_action = 0
+
+    def act(self, obs, reward: float) -> int:
+        """agent_train.py:24-37.  The two numpy global-RNG draws happen on the host in the reference's
+        order (np.random.random(), then np.random.choice over the legal slots when exploring), so a
+        seeded run makes the same explore/exploit choices as the reference."""
+        n = 1
+        s = self._session(n)
+        self._feature_extractor.pack([obs], out=s.packed)
+        packed = s.packed[0].copy()
+        n_act = int(packed["n_act"])
+        action_mask = np.zeros((self._feature_extractor.output_dim,), dtype=np.int32)
+        action_mask[:n_act] = 1
+        if self._last_state is not None:
+            self._replay_buffer.append(
+                ReplayBufferItem(self._last_state, self._last_action_mask, self._last_action, packed, action_mask,
+                                 reward))
+        if np.random.random() < self._epsilon:
+            action = self._act_random(None, action_mask)
+        else:
+            q, a = s.decide(n)
+            action = int(a[0])
+            self._log_q(q[0], n_act, action)
+        self._last_state = packed
+        self._last_action_mask = action_mask
+        self._last_action = action
+        return action
+
+    def stop_episode(self, reward: float) -> None:
+        self._replay_buffer.append(
+            ReplayBufferItem(self._last_state, self._last_action_mask, self._last_action, None, None, reward))
+        self._last_state = None
+        self._last_action_mask = None
+        self._last_action = 0

@@ -328,7 +328,8 @@ struct pk_session {
   float* d_u_explore;
   float* d_u_pick;
   float* d_params;
-  float* d_prepared;
+  float* d_prepared;        // owned copy (pk_session_load_weights)
+  const float* prepared;    // what the kernels read: d_prepared or the caller's buffer
 };
 
 extern "C" void pk_session_destroy(pk_session* s) {
@@ -383,6 +384,7 @@ extern "C" int pk_session_load_weights(pk_session* s, const pk_mlp* hm) {
   cudaFree(s->d_params);
   cudaFree(s->d_prepared);
   s->d_params = s->d_prepared = nullptr;
+  s->prepared = nullptr;
   PK_CUDA(cudaMalloc(&s->d_params, (size_t)P.total * sizeof(float)));
   PK_CUDA(cudaMalloc(&s->d_prepared, (size_t)lay.total * sizeof(float)));
   pk_mlp dm = *hm;
@@ -405,6 +407,18 @@ extern "C" int pk_session_load_weights(pk_session* s, const pk_mlp* hm) {
   PK_CUDA(cudaStreamSynchronize(s->stream));
   s->n_layers = hm->n_layers;
   s->n_channels = hm->n_channels;
+  s->prepared = s->d_prepared;
+  return PK_OK;
+}
+
+extern "C" int pk_session_use_prepared(pk_session* s, const float* prepared_dev, int n_layers, int n_channels) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(s != nullptr && prepared_dev != nullptr, "pk_session_use_prepared: null argument");
+  PK_REQUIRE(n_layers >= 1 && n_layers <= PK_MAX_LAYERS && n_channels >= 1, "bad network shape");
+  PK_REQUIRE(aligned16(prepared_dev), "prepared weights must be 16-byte aligned");
+  s->prepared = prepared_dev;
+  s->n_layers = n_layers;
+  s->n_channels = n_channels;
   return PK_OK;
 }
 
@@ -413,7 +427,7 @@ extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, 
                                       float* q_host, int32_t* action_host) {
   PK_CHECK_INIT();
   PK_REQUIRE(s != nullptr && packed_host != nullptr, "pk_session_decide_host: null argument");
-  PK_REQUIRE(s->d_prepared != nullptr, "pk_session_decide_host: no weights loaded");
+  PK_REQUIRE(s->prepared != nullptr, "pk_session_decide_host: no weights loaded");
   PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
   if (B == 0) return PK_OK;
   PK_CUDA(cudaMemcpyAsync(s->d_packed, packed_host, (size_t)B * sizeof(pk_obs), cudaMemcpyHostToDevice, s->stream));
@@ -432,7 +446,7 @@ extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, 
     PK_CUDA(cudaMemcpyAsync(s->d_u_pick, u_pick_host, (size_t)B * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     sp.u_pick = s->d_u_pick;
   }
-  int rc = pk_decide_impl(s->d_packed, B, s->A, s->d_prepared, s->n_layers, s->n_channels, s->d_feat, s->d_mask, s->d_q,
+  int rc = pk_decide_impl(s->d_packed, B, s->A, s->prepared, s->n_layers, s->n_channels, s->d_feat, s->d_mask, s->d_q,
                           s->d_action, &sp, s->stream);
   if (rc) return rc;
   if (q_host) PK_CUDA(cudaMemcpyAsync(q_host, s->d_q, (size_t)B * s->A * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
@@ -440,6 +454,35 @@ extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, 
     PK_CUDA(cudaMemcpyAsync(action_host, s->d_action, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
   PK_CUDA(cudaStreamSynchronize(s->stream));
   return PK_OK;
+}
+
+extern "C" int pk_session_fetch(pk_session* s, int B, float* feat_host, int32_t* mask_host) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(s != nullptr, "pk_session_fetch: null session");
+  PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
+  if (B == 0) return PK_OK;
+  if (feat_host) {
+    PK_REQUIRE(s->d_feat != nullptr, "this session does not materialise features");
+    PK_CUDA(cudaMemcpyAsync(feat_host, s->d_feat, (size_t)B * g.tab.C * s->A * sizeof(float), cudaMemcpyDeviceToHost,
+                            s->stream));
+  }
+  if (mask_host)
+    PK_CUDA(cudaMemcpyAsync(mask_host, s->d_mask, (size_t)B * s->A * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+  PK_CUDA(cudaStreamSynchronize(s->stream));
+  return PK_OK;
+}
+
+extern "C" int pk_session_encode_host(pk_session* s, const pk_obs* packed_host, int B, float* feat_host,
+                                      int32_t* mask_host) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(s != nullptr && packed_host != nullptr, "pk_session_encode_host: null argument");
+  PK_REQUIRE(s->d_feat != nullptr, "this session does not materialise features");
+  PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
+  if (B == 0) return PK_OK;
+  PK_CUDA(cudaMemcpyAsync(s->d_packed, packed_host, (size_t)B * sizeof(pk_obs), cudaMemcpyHostToDevice, s->stream));
+  int rc = pk_decide_impl(s->d_packed, B, s->A, nullptr, 0, 0, s->d_feat, s->d_mask, nullptr, nullptr, nullptr, s->stream);
+  if (rc) return rc;
+  return pk_session_fetch(s, B, feat_host, mask_host);
 }
 
 extern "C" const float* pk_session_features(const pk_session* s) { return s ? s->d_feat : nullptr; }
