@@ -51,12 +51,15 @@ struct PkDeviceTables {
 //   w1t  [C+1][HP]  row k = input channel k, row C = zeros (target of "no row" gathers)
 //   b[0] [HP]
 //   wl[l] [HP][HP] (l = 1..n_layers-1), b[l] [HP]
-//   wout [HP], bout [4]
+//   wout [HP], bout [4]                                   <- `total` ends here (what inference reads)
+//   wn[l] [HP][HP] (l = 1..n_layers-1): the same hidden matrices NOT transposed, row j = output channel,
+//                  read by the backward pass (dh = W^T dz)           <- `total_train` ends here
 struct PkLayout {
   int C, H, HP, n_layers;
-  unsigned w1t, wout, bout, total;
+  unsigned w1t, wout, bout, total, total_train;
   unsigned b[PK_MAX_LAYERS];
   unsigned wl[PK_MAX_LAYERS];
+  unsigned wn[PK_MAX_LAYERS];
 };
 
 __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
@@ -87,8 +90,23 @@ __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
   L.bout = o;
   o += 4;
   L.total = o;
+  for (int l = 0; l < PK_MAX_LAYERS; ++l) {
+    if (l >= 1 && l < n_layers) {
+      L.wn[l] = o;
+      o += (unsigned)L.HP * L.HP;
+    } else {
+      L.wn[l] = 0;
+    }
+  }
+  L.total_train = o;
   return L;
 }
+
+// flat parameter index (state_dict order) -> offset in the prepared layout; *wn_off = offset of the
+// untransposed copy for hidden-layer weights, 0 otherwise
+struct PkParamLayout;
+__host__ __device__ inline unsigned pk_flat_to_prepared(const PkParamLayout& P, const PkLayout& L, unsigned i,
+                                                        unsigned* wn_off);
 
 // Flat parameter vector in state_dict order (layers.i.weight, layers.i.bias, ..., output.weight, output.bias)
 struct PkParamLayout {
@@ -119,6 +137,22 @@ __host__ __device__ inline PkParamLayout pk_make_param_layout(int n_layers, int 
   o += 1;
   P.total = o;
   return P;
+}
+
+__host__ __device__ inline unsigned pk_flat_to_prepared(const PkParamLayout& P, const PkLayout& L, unsigned i,
+                                                        unsigned* wn_off) {
+  *wn_off = 0;
+  for (int l = 0; l < P.n_layers; ++l) {
+    if (i < P.b[l]) {
+      const unsigned e = i - P.w[l], cin = l == 0 ? (unsigned)P.C : (unsigned)P.H;
+      const unsigned j = e / cin, k = e - j * cin;
+      if (l > 0) *wn_off = L.wn[l] + j * L.HP + k;
+      return (l == 0 ? L.w1t : L.wl[l]) + k * L.HP + j;
+    }
+    if (i < P.b[l] + (unsigned)P.H) return L.b[l] + (i - P.b[l]);
+  }
+  if (i < P.bout) return L.wout + (i - P.wout);
+  return L.bout;
 }
 
 struct PkSelect {

@@ -626,6 +626,13 @@ __global__ void pk_transpose_pad_kernel(const float* __restrict__ src, float* __
   const int k = (int)(i / HP), j = (int)(i - (long long)k * HP);
   dst[i] = (k < cols_in && j < rows_out) ? src[(size_t)j * cols_in + k] : 0.0f;
 }
+// src (rows, cols) row-major -> dst [HP][HP] zero padded, same orientation
+__global__ void pk_pad2d_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int cols, int HP) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)HP * HP) return;
+  const int j = (int)(i / HP), k = (int)(i - (long long)j * HP);
+  dst[i] = (j < rows && k < cols) ? src[(size_t)j * cols + k] : 0.0f;
+}
 __global__ void pk_copy_pad_kernel(const float* __restrict__ src, float* __restrict__ dst, int n, int n_pad) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_pad) dst[i] = i < n ? src[i] : 0.0f;

@@ -100,7 +100,7 @@ extern "C" int pk_sm_count(void) { return g.device < 0 ? 0 : g.sm_count; }
 // ---- weights --------------------------------------------------------------------------------------
 extern "C" size_t pk_mlp_prepared_floats(int n_layers, int n_channels, int in_channels) {
   if (n_layers < 1 || n_layers > PK_MAX_LAYERS || n_channels < 1 || in_channels < 1) return 0;
-  return pk_make_layout(n_layers, n_channels, in_channels).total;
+  return pk_make_layout(n_layers, n_channels, in_channels).total_train;
 }
 extern "C" size_t pk_mlp_param_floats(int n_layers, int n_channels, int in_channels) {
   if (n_layers < 1 || n_layers > PK_MAX_LAYERS || n_channels < 1 || in_channels < 1) return 0;
@@ -118,6 +118,8 @@ static int pk_prepare_impl(const pk_mlp* m, float* prepared, cudaStream_t st) {
     const long long n = (long long)rows * HP;
     pk_transpose_pad_kernel<<<(unsigned)((n + T - 1) / T), T, 0, st>>>(m->w[l], dst, H, cin, rows, HP);
     pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->b[l], prepared + lay.b[l], H, HP);
+    if (l > 0)  // untransposed padded copy for the backward pass
+      pk_pad2d_kernel<<<(unsigned)(((long long)HP * HP + T - 1) / T), T, 0, st>>>(m->w[l], prepared + lay.wn[l], H, H, HP);
   }
   PK_REQUIRE(m->w_out != nullptr && m->b_out != nullptr, "pk_mlp_prepare: null output tensor");
   pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->w_out, prepared + lay.wout, H, HP);
@@ -386,7 +388,7 @@ extern "C" int pk_session_load_weights(pk_session* s, const pk_mlp* hm) {
   s->d_params = s->d_prepared = nullptr;
   s->prepared = nullptr;
   PK_CUDA(cudaMalloc(&s->d_params, (size_t)P.total * sizeof(float)));
-  PK_CUDA(cudaMalloc(&s->d_prepared, (size_t)lay.total * sizeof(float)));
+  PK_CUDA(cudaMalloc(&s->d_prepared, (size_t)lay.total_train * sizeof(float)));
   pk_mlp dm = *hm;
   const int H = hm->n_channels;
   for (int l = 0; l < hm->n_layers; ++l) {

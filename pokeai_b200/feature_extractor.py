@@ -99,8 +99,10 @@ class FeatureExtractor:
         if isinstance(obs_list, np.ndarray) and obs_list.dtype == PK_OBS_DTYPE:
             if out is None:
                 return obs_list
-            out[:len(obs_list)] = obs_list
-            return out[:len(obs_list)]
+            n = len(obs_list)
+            # byte copy: numpy assigns structured records field by field, which is ~20x slower
+            out[:n].view(np.uint8)[...] = np.ascontiguousarray(obs_list).view(np.uint8)
+            return out[:n]
         n = len(obs_list)
         rec = out[:n] if out is not None else np.zeros(n, dtype=PK_OBS_DTYPE)
         if out is not None:
