@@ -186,16 +186,19 @@ typedef struct pk_batch {
 } pk_batch;
 
 PK_API size_t pk_mlp_param_floats(int n_layers, int n_channels, int in_channels);
-/* scratch floats pk_dqn_grad needs (per-CTA partial gradients) */
-PK_API size_t pk_dqn_scratch_floats(int n_layers, int n_channels, int in_channels);
-/* Forward x3, TD target, Huber, backward.  Writes grad (flat, pre-clamp, already divided by
- * n_global) and adds this batch's loss contribution to *loss_sum (caller zeroes it).
- * prepared_target is the prepared copy of the target network. */
+/* scratch floats pk_dqn_grad needs for batches of up to n_max transitions (next-state Q values, per-CTA partial
+ * gradients).  Call after pk_init. */
+PK_API size_t pk_dqn_scratch_floats(int n_layers, int n_channels, int in_channels, int n_max);
+/* Forwards over next_state (online argmax + target Q, or target max when double_dqn == 0), Q(s)[a], TD target,
+ * Huber, backward.  Writes grad (flat, pre-clamp, = d/dparams of sum_i huber_i / n_global) and
+ * *loss = sum_i huber_i / n_global (device pointer, may be NULL).  prepared / prepared_target are the prepared
+ * copies of the online and target networks.  Deterministic (fixed summation order) when the one-hot
+ * accumulator fits in shared memory (<= 64 channels, <= 3 layers). */
 PK_API int pk_dqn_grad(const float* prepared, const float* prepared_target, int n_layers, int n_channels, int A,
-                const pk_batch* batch, float gamma, int double_dqn, float* grad, float* loss_sum,
+                const pk_batch* batch, float gamma, int double_dqn, float* grad, float* loss,
                 float* scratch, void* stream);
 /* clamp(grad, -1, 1) then Adam (torch defaults, no weight decay) on the flat parameter
- * vector, then refresh `prepared` from the new parameters.  step is 1-based. */
+ * vector; also writes the new values into `prepared` (may be NULL).  step is 1-based. */
 PK_API int pk_clamp_adam(float* params, const float* grad, float* exp_avg, float* exp_avg_sq, int n_layers,
                   int n_channels, int in_channels, float lr, float beta1, float beta2, float eps, int step,
                   float* prepared, void* stream);

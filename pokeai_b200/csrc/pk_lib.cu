@@ -2,6 +2,7 @@
 // .cuh files included below so that the __constant__ tables are shared without -rdc.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>

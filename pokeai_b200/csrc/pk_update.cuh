@@ -1,3 +1,363 @@
-// DQN minibatch update kernels (trainer.py:152-198) -- filled in below.
+// DQN minibatch update kernels (reference: pokeai/ai/generic_move_model/trainer.py:152-198).
+//
+// Transitions arrive packed (two 144-byte records each) and are re-encoded on the fly; the dense
+// (617, A) feature tensors of the reference are never built.  One update is
+//
+//   pk_decide(next_state, online)  -> a* = argmax over legal slots            (trainer.py:171-174)
+//   pk_decide(next_state, target)  -> Q_target(s', .)                         (trainer.py:175-182)
+//   pk_dqn_backward_kernel         -> Q(s)[a] (only the chosen column carries loss: gather, :163),
+//                                     y = gamma v + r (:184), Huber (:187), backward (:192) with
+//                                     per-CTA partial gradients
+//   pk_dqn_reduce_kernel / pk_dqn_flat_kernel -> fixed-order sum over CTAs, state_dict-ordered flat gradient
+//   pk_clamp_adam_kernel           -> clamp to [-1, 1] (:193-194), Adam (:195), refresh of the prepared weights
+//
+// pk_dqn_backward_kernel: one persistent CTA per SM, 16 warps.  Per tile of 16 transitions:
+//   phase 1  warp w runs transition w forward (layer 0 in gather form, hidden layers from shared memory) and
+//            backward down to dz of every layer, leaving x (sparse), h_l and dz_l in the tile buffer;
+//   phase 2  all 512 threads accumulate weight gradients into accumulators they OWN: registers for the dense
+//            tensors (hidden matrices, biases, head, the 50 state rows of W0), shared memory for the one-hot
+//            rows of W0 (each warp owns the rows r with r % 16 == warp).  No atomics, fixed order: the
+//            gradient is bit-reproducible run to run.
+// If the one-hot accumulator (567 x HP floats) does not fit beside the weights, that part alone falls back to
+// red.global.add.f32 on the output buffer (SPARSE_SMEM = false).
 #pragma once
 #include "pk_common.cuh"
+
+#define PK_UPD_TILE 16
+#define PK_UPD_THREADS 512
+#define PK_UPD_FIXED 112  // floats per tile record before h/dz: rec[36] sv[64] idx[8] g[4]
+#define PK_UPD_MAX_LAYERS 4
+
+struct PkUpdPlan {
+  unsigned tail, wn, w1s, tile, tile_stride, gacc, total;  // byte offsets except tile_stride (floats)
+};
+
+__host__ __device__ inline PkUpdPlan pk_upd_plan(const PkLayout& lay, bool sparse_smem) {
+  PkUpdPlan p;
+  unsigned o = 0;
+  p.tail = o;
+  o += (lay.total - lay.b[0]) * 4u;
+  p.wn = o;
+  o += (lay.total_train - lay.total) * 4u;
+  p.w1s = o;
+  o += (unsigned)PK_N_STATE * lay.HP * 4u;
+  p.tile = o;
+  p.tile_stride = PK_UPD_FIXED + 2u * lay.n_layers * lay.HP;
+  o += p.tile_stride * PK_UPD_TILE * 4u;
+  o = (o + 15u) & ~15u;
+  p.gacc = o;
+  if (sparse_smem) o += (unsigned)(lay.C - PK_N_STATE) * lay.HP * 4u;
+  p.total = o;
+  return p;
+}
+
+// acc[0..CPL) += sum_k M[k][lane's channels] * x[k]   (M and x in shared memory, HP x HP)
+template <int CPL>
+__device__ __forceinline__ void pk_matvec_smem(const float* M, const float* x, float (&acc)[CPL], int lane) {
+  constexpr int HP = 32 * CPL;
+#pragma unroll 4
+  for (int k = 0; k < HP; k += 4) {
+    const float4 xv = *reinterpret_cast<const float4*>(x + k);
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      float w[CPL];
+      pk_lds_vec<CPL>(M + (k + kk) * HP, lane, w);
+      pk_fma_vec<CPL>(acc, w, kk == 0 ? xv.x : kk == 1 ? xv.y : kk == 2 ? xv.z : xv.w);
+    }
+  }
+}
+
+struct PkUpdArgs {
+  const uint4* state;
+  const uint4* next_state;
+  const int* action;
+  const float* reward;
+  const uint8_t* terminal;
+  const int* a_star;      // [n] online argmax over legal next actions (double DQN), may be null otherwise
+  const float* q_target;  // [n][A] target network on next_state
+  int n, A, double_dqn;
+  float inv_n, gamma;
+};
+
+template <int CPL, int NL, bool SPARSE_SMEM>
+__global__ void __launch_bounds__(PK_UPD_THREADS, 1)
+pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay, float* __restrict__ partial,
+                       float* __restrict__ gsum) {
+  constexpr int HP = 32 * CPL;
+  constexpr int EPT = HP * HP / PK_UPD_THREADS;                                   // hidden-matrix entries per thread
+  constexpr int NS = (PK_N_STATE * HP + PK_UPD_THREADS - 1) / PK_UPD_THREADS;    // state-row entries per thread
+  static_assert(EPT >= 1 && HP % EPT == 0, "hidden matrix must split evenly over the CTA");
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const PkUpdPlan plan = pk_upd_plan(lay, SPARSE_SMEM);
+  float* s_tail = reinterpret_cast<float*>(smem + plan.tail);
+  float* s_wn = reinterpret_cast<float*>(smem + plan.wn);
+  float* s_w1s = reinterpret_cast<float*>(smem + plan.w1s);
+  float* s_tile = reinterpret_cast<float*>(smem + plan.tile);
+  float* s_gacc = reinterpret_cast<float*>(smem + plan.gacc);
+  const unsigned tbase = lay.b[0];
+  const int zero_row = lay.C;
+
+  {  // stage the small tensors; zero the one-hot accumulator
+    const float4* st = reinterpret_cast<const float4*>(prep + lay.b[0]);
+    float4* dt = reinterpret_cast<float4*>(s_tail);
+    for (int i = tid; i < (int)((lay.total - lay.b[0]) >> 2); i += PK_UPD_THREADS) dt[i] = __ldg(st + i);
+    const float4* sn = reinterpret_cast<const float4*>(prep + lay.total);
+    float4* dn = reinterpret_cast<float4*>(s_wn);
+    for (int i = tid; i < (int)((lay.total_train - lay.total) >> 2); i += PK_UPD_THREADS) dn[i] = __ldg(sn + i);
+    const float4* sw = reinterpret_cast<const float4*>(prep + lay.w1t);
+    float4* dw = reinterpret_cast<float4*>(s_w1s);
+    for (int i = tid; i < (PK_N_STATE * HP) >> 2; i += PK_UPD_THREADS) dw[i] = __ldg(sw + i);
+    if (SPARSE_SMEM) {
+      float4* z = reinterpret_cast<float4*>(s_gacc);
+      for (int i = tid; i < ((lay.C - PK_N_STATE) * HP) >> 2; i += PK_UPD_THREADS) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  __syncthreads();
+
+  // ---- accumulators this thread owns ------------------------------------------------------------------
+  float acc_w[NL > 1 ? NL - 1 : 1][EPT];
+  float acc_b[NL];
+  float acc_s[NS];
+  float acc_wout = 0.f, acc_bout = 0.f, acc_loss = 0.f;
+#pragma unroll
+  for (int l = 0; l < (NL > 1 ? NL - 1 : 1); ++l)
+#pragma unroll
+    for (int i = 0; i < EPT; ++i) acc_w[l][i] = 0.f;
+#pragma unroll
+  for (int l = 0; l < NL; ++l) acc_b[l] = 0.f;
+#pragma unroll
+  for (int i = 0; i < NS; ++i) acc_s[i] = 0.f;
+  const int own_k = (tid * EPT) / HP, own_j0 = (tid * EPT) % HP;
+
+  float* T = s_tile + warp * plan.tile_stride;  // this warp's tile record
+  uint4* rec = reinterpret_cast<uint4*>(T);
+  const uint8_t* r = reinterpret_cast<const uint8_t*>(T);
+  float* sv = T + 36;
+  int* idx = reinterpret_cast<int*>(T + 100);
+  float* gl = T + 108;
+  float* hb = T + PK_UPD_FIXED;            // h[l] = output of layer l (post-ReLU), l = 0..NL-1
+  float* dzb = hb + NL * HP;               // dz[l] = dLoss/d(pre-activation of layer l)
+  const float* w1t = prep + lay.w1t;
+
+  for (int t0 = blockIdx.x * PK_UPD_TILE; t0 < a.n; t0 += gridDim.x * PK_UPD_TILE) {
+    const int nt = min(PK_UPD_TILE, a.n - t0);
+    // ================= phase 1: one transition per warp =================
+    if (warp < nt) {
+      const long long i = t0 + warp;
+      if (lane < 9) rec[lane] = __ldg(a.state + i * 9 + lane);
+      __syncwarp();
+      const int act = a.action[i];
+      sv[lane] = pk_state_feature(r, lane);
+      sv[lane + 32] = pk_state_feature(r, lane + 32);
+      if (lane < 8) {
+        const int row = (act >= 0 && act < PK_MAX_ACTIONS) ? pk_choice_row(r, act, lane) : -1;
+        idx[lane] = row < 0 ? zero_row : row;
+      }
+      __syncwarp();
+      // ---- forward, chosen column only (state_action_values = model(s).gather(1, a), trainer.py:163) ----
+      float z[CPL];
+      pk_lds_vec<CPL>(s_tail, lane, z);  // b0
+#pragma unroll 1
+      for (int k4 = 0; k4 < 52; k4 += 4) {
+        const float4 s4 = *reinterpret_cast<const float4*>(sv + k4);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const float x = kk == 0 ? s4.x : kk == 1 ? s4.y : kk == 2 ? s4.z : s4.w;
+          if (x != 0.0f) {
+            float w[CPL];
+            pk_lds_vec<CPL>(s_w1s + (k4 + kk) * HP, lane, w);
+            pk_fma_vec<CPL>(z, w, x);
+          }
+        }
+      }
+      {
+        float gr[8][CPL];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) pk_ldg_vec<CPL>(w1t + (size_t)idx[s] * HP, lane, gr[s]);
+#pragma unroll
+        for (int s = 0; s < 8; ++s)
+#pragma unroll
+          for (int c = 0; c < CPL; ++c) z[c] += gr[s][c];
+      }
+      float h[CPL];
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) h[c] = fmaxf(z[c], 0.f);
+      pk_sts_vec<CPL>(hb, lane, h);
+#pragma unroll
+      for (int l = 1; l < NL; ++l) {
+        __syncwarp();
+        pk_lds_vec<CPL>(s_tail + (lay.b[l] - tbase), lane, z);
+        pk_matvec_smem<CPL>(s_tail + (lay.wl[l] - tbase), hb + (l - 1) * HP, z, lane);
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) h[c] = fmaxf(z[c], 0.f);
+        pk_sts_vec<CPL>(hb + l * HP, lane, h);
+      }
+      float wo[CPL];
+      pk_lds_vec<CPL>(s_tail + (lay.wout - tbase), lane, wo);
+      float q = 0.f;
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) q = fmaf(wo[c], h[c], q);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      q += s_tail[lay.bout - tbase];
+      // ---- TD target (trainer.py:164-184) ----
+      float v = 0.f;
+      if (!a.terminal[i]) {
+        if (a.double_dqn) {
+          v = a.q_target[i * a.A + a.a_star[i]];
+        } else {
+          const uint4 w1 = __ldg(a.next_state + i * 9 + 1);
+          const int n_next = min((int)((w1.w >> 16) & 0xffu), a.A);
+          v = -CUDART_INF_F;
+          for (int c = 0; c < n_next; ++c) v = fmaxf(v, a.q_target[i * a.A + c]);
+        }
+      }
+      const float y = __fadd_rn(__fmul_rn(v, a.gamma), a.reward[i]);
+      const float d = q - y;
+      const float ad = fabsf(d);
+      const float li = ad < 1.0f ? 0.5f * d * d : ad - 0.5f;        // smooth_l1, beta = 1 (trainer.py:187)
+      const float g = fminf(fmaxf(d, -1.0f), 1.0f) * a.inv_n;        // d(mean Huber)/dq
+      if (lane == 0) {
+        gl[0] = g;
+        gl[1] = li * a.inv_n;
+      }
+      // ---- backward to the pre-activations of every layer ----
+      float dz[CPL];
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) dz[c] = h[c] > 0.f ? g * wo[c] : 0.f;
+      pk_sts_vec<CPL>(dzb + (NL - 1) * HP, lane, dz);
+#pragma unroll
+      for (int l = NL - 1; l >= 1; --l) {
+        __syncwarp();
+        float dh[CPL], hp[CPL];
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) dh[c] = 0.f;
+        pk_matvec_smem<CPL>(s_wn + (lay.wn[l] - lay.total), dzb + l * HP, dh, lane);  // dh = W_l^T dz_l
+        pk_lds_vec<CPL>(hb + (l - 1) * HP, lane, hp);
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) dz[c] = hp[c] > 0.f ? dh[c] : 0.f;
+        pk_sts_vec<CPL>(dzb + (l - 1) * HP, lane, dz);
+      }
+    }
+    __syncthreads();
+    // ================= phase 2: owned accumulation over the tile =================
+    for (int t = 0; t < nt; ++t) {
+      const float* R = s_tile + t * plan.tile_stride;
+      const float* Rh = R + PK_UPD_FIXED;
+      const float* Rdz = Rh + NL * HP;
+      if (tid < HP) {
+        acc_wout = fmaf(R[108], Rh[(NL - 1) * HP + tid], acc_wout);
+#pragma unroll
+        for (int l = 0; l < NL; ++l) acc_b[l] += Rdz[l * HP + tid];
+      }
+      if (tid == 0) {
+        acc_bout += R[108];
+        acc_loss += R[109];
+      }
+#pragma unroll
+      for (int l = 1; l < NL; ++l) {
+        const float hk = Rh[(l - 1) * HP + own_k];
+#pragma unroll
+        for (int i = 0; i < EPT; ++i) acc_w[l - 1][i] = fmaf(hk, Rdz[l * HP + own_j0 + i], acc_w[l - 1][i]);
+      }
+#pragma unroll
+      for (int i = 0; i < NS; ++i) {
+        const int e = tid + PK_UPD_THREADS * i;
+        if (e < PK_N_STATE * HP) acc_s[i] = fmaf(R[36 + e / HP], Rdz[e % HP], acc_s[i]);
+      }
+    }
+    // one-hot rows of W0: warp w owns rows with (row & 15) == w; pairs (t, slot) scanned 32 at a time
+    for (int p0 = 0; p0 < nt * 8; p0 += 32) {
+      const int p = p0 + lane;
+      int row = zero_row;
+      if (p < nt * 8) row = reinterpret_cast<const int*>(s_tile + (p >> 3) * plan.tile_stride + 100)[p & 7];
+      unsigned mine = __ballot_sync(0xffffffffu, row != zero_row && (row & 15) == warp);
+      while (mine) {
+        const int src = __ffs(mine) - 1;
+        mine &= mine - 1u;
+        const int rr = __shfl_sync(0xffffffffu, row, src);
+        const float* Rdz0 = s_tile + ((p0 + src) >> 3) * plan.tile_stride + PK_UPD_FIXED + NL * HP;
+        float dz[CPL];
+        pk_lds_vec<CPL>(Rdz0, lane, dz);
+        if (SPARSE_SMEM) {
+          float* dst = s_gacc + (rr - PK_N_STATE) * HP;
+          float cur[CPL];
+          pk_lds_vec<CPL>(dst, lane, cur);
+#pragma unroll
+          for (int c = 0; c < CPL; ++c) cur[c] += dz[c];
+          pk_sts_vec<CPL>(dst, lane, cur);
+        } else {
+#pragma unroll
+          for (int c = 0; c < CPL; ++c) atomicAdd(gsum + lay.w1t + (size_t)rr * HP + CPL * lane + c, dz[c]);
+        }
+      }
+    }
+    __syncthreads();  // the tile buffer is rewritten by the next tile's phase 1
+  }
+
+  // ---- this CTA's partial gradient, prepared layout (every position of [0, lay.total) written once) ----
+  float* out = partial + (size_t)blockIdx.x * lay.total;
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    const int e = tid + PK_UPD_THREADS * i;
+    if (e < PK_N_STATE * HP) out[lay.w1t + e] = acc_s[i];
+  }
+  for (int e = tid; e < (lay.C - PK_N_STATE) * HP; e += PK_UPD_THREADS)
+    out[lay.w1t + PK_N_STATE * HP + e] = SPARSE_SMEM ? s_gacc[e] : 0.f;
+  if (tid < HP) {
+    out[lay.w1t + (size_t)lay.C * HP + tid] = 0.f;  // the zero row stays zero
+    out[lay.wout + tid] = acc_wout;
+#pragma unroll
+    for (int l = 0; l < NL; ++l) out[lay.b[l] + tid] = acc_b[l];
+  }
+#pragma unroll
+  for (int l = 1; l < NL; ++l)
+#pragma unroll
+    for (int i = 0; i < EPT; ++i) out[lay.wl[l] + own_k * HP + own_j0 + i] = acc_w[l - 1][i];
+  if (tid < 4) out[lay.bout + tid] = tid == 0 ? acc_bout : tid == 1 ? acc_loss : 0.f;
+}
+
+// gsum[p] (+)= sum over CTAs of partial[cta][p], in CTA order (deterministic)
+__global__ void pk_dqn_reduce_kernel(const float* __restrict__ partial, int n_cta, unsigned total, float* __restrict__ gsum,
+                                     int accumulate) {
+  const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= total) return;
+  float s = accumulate ? gsum[p] : 0.f;
+  for (int c = 0; c < n_cta; ++c) s += partial[(size_t)c * total + p];
+  gsum[p] = s;
+}
+
+// prepared-layout sums -> flat state_dict-ordered gradient (+ the loss)
+__global__ void pk_dqn_flat_kernel(const float* __restrict__ gsum, PkParamLayout P, PkLayout lay, float* __restrict__ grad,
+                                   float* __restrict__ loss) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0 && loss != nullptr) *loss = gsum[lay.bout + 1];
+  if (i >= P.total) return;
+  unsigned wn;
+  grad[i] = gsum[pk_flat_to_prepared(P, lay, i, &wn)];
+}
+
+// clamp(grad) -> Adam (torch.optim.Adam defaults: no weight decay, no amsgrad) -> params, and the prepared copies
+struct PkAdam {
+  float one_minus_b1, b2, one_minus_b2, step_size, bc2_sqrt, eps;
+};
+__global__ void pk_clamp_adam_kernel(float* __restrict__ params, const float* __restrict__ grad, float* __restrict__ m,
+                                     float* __restrict__ v, PkParamLayout P, PkLayout lay, PkAdam h,
+                                     float* __restrict__ prepared) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P.total) return;
+  const float g = fminf(fmaxf(grad[i], -1.0f), 1.0f);            // trainer.py:193-194
+  const float mi = m[i] + (g - m[i]) * h.one_minus_b1;            // exp_avg.lerp_(grad, 1 - beta1)
+  const float vi = v[i] * h.b2 + (h.one_minus_b2 * g) * g;        // exp_avg_sq.mul_(beta2).addcmul_(g, g, 1 - beta2)
+  const float denom = sqrtf(vi) / h.bc2_sqrt + h.eps;
+  const float p = params[i] + (-h.step_size * mi) / denom;        // param.addcdiv_(exp_avg, denom, value=-step_size)
+  m[i] = mi;
+  v[i] = vi;
+  params[i] = p;
+  if (prepared != nullptr) {
+    unsigned wn;
+    prepared[pk_flat_to_prepared(P, lay, i, &wn)] = p;
+    if (wn) prepared[wn] = p;
+  }
+}

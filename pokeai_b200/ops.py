@@ -169,3 +169,59 @@ def prepare_from_flat(flat: torch.Tensor, n_layers: int, H: int, Cin: int, out: 
     m.b_out = base + 4 * off
     N.check(N.lib().pk_mlp_prepare(C.byref(m), prepared.data_ptr(), _stream_ptr(dev)))
     return prepared
+
+
+# ---- DQN update (trainer.py:152-198) ------------------------------------------------------------------------
+def dqn_grad(prepared: torch.Tensor, prepared_target: torch.Tensor, n_layers: int, n_channels_: int, A: int,
+             state: torch.Tensor, next_state: torch.Tensor, action: torch.Tensor, reward: torch.Tensor,
+             terminal: torch.Tensor, gamma: float, double_dqn: bool = True, n_global: Optional[int] = None,
+             scratch: Optional[torch.Tensor] = None):
+    """Packed transitions (device) -> (flat pre-clamp gradient in state_dict order, loss (1,) tensor).
+    state / next_state: (n, 144) uint8; action (n,) int32; reward (n,) fp32; terminal (n,) uint8."""
+    dev = _dev(state)
+    n = _check_packed(state)
+    assert _check_packed(next_state) == n
+    assert action.dtype == torch.int32 and reward.dtype == torch.float32 and terminal.dtype == torch.uint8
+    assert action.numel() == n and reward.numel() == n and terminal.numel() == n
+    Cn = n_channels()
+    lib = N.lib()
+    if scratch is None:
+        scratch = torch.empty(lib.pk_dqn_scratch_floats(n_layers, n_channels_, Cn, n), dtype=torch.float32, device=dev)
+    grad = torch.empty(lib.pk_mlp_param_floats(n_layers, n_channels_, Cn), dtype=torch.float32, device=dev)
+    loss = torch.zeros(1, dtype=torch.float32, device=dev)
+    b = N.pk_batch()
+    b.n, b.n_global = n, (n if n_global is None else int(n_global))
+    b.state, b.next_state = state.data_ptr(), next_state.data_ptr()
+    b.action, b.reward, b.terminal = action.data_ptr(), reward.data_ptr(), terminal.data_ptr()
+    N.check(lib.pk_dqn_grad(prepared.data_ptr(), prepared_target.data_ptr(), n_layers, n_channels_, A, C.byref(b),
+                            float(gamma), 1 if double_dqn else 0, grad.data_ptr(), loss.data_ptr(), scratch.data_ptr(),
+                            _stream_ptr(dev)))
+    return grad, loss
+
+
+def clamp_adam(params: torch.Tensor, grad: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor,
+               n_layers: int, n_channels_: int, step: int, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+               prepared: Optional[torch.Tensor] = None) -> None:
+    """In place: clamp(grad, -1, 1), Adam step on the flat parameter vector, refresh of `prepared`."""
+    dev = _dev(params)
+    for t in (params, grad, exp_avg, exp_avg_sq):
+        assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == params.numel()
+    N.check(N.lib().pk_clamp_adam(params.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+                                  n_layers, n_channels_, n_channels(), float(lr), float(betas[0]), float(betas[1]),
+                                  float(eps), int(step), prepared.data_ptr() if prepared is not None else None,
+                                  _stream_ptr(dev)))
+
+
+def unflatten(flat: torch.Tensor, n_layers: int, H: int, Cin: int) -> dict:
+    """Flat parameter / gradient vector -> dict with the reference's state_dict keys and shapes."""
+    out, off = {}, 0
+    for i in range(n_layers):
+        cin = Cin if i == 0 else H
+        out[f"layers.{i}.weight"] = flat[off:off + H * cin].view(H, cin, 1)
+        off += H * cin
+        out[f"layers.{i}.bias"] = flat[off:off + H]
+        off += H
+    out["output.weight"] = flat[off:off + H].view(1, H, 1)
+    off += H
+    out["output.bias"] = flat[off:off + 1]
+    return out

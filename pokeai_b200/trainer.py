@@ -1,0 +1,343 @@
+"""Trainer: the reference's DQN trainer interface (pokeai/ai/generic_move_model/trainer.py:15-198) on the
+B200 update kernels.
+
+Same constructor, attributes, schedule (``train``), checkpoint dictionaries (``save_state`` / ``load_state``)
+and agent factories as the reference.  What changes underneath:
+  * parameters, gradients and Adam moments live in flat fp32 CUDA vectors (state_dict order); ``self.model`` /
+    ``self.target_model`` are MLPModel modules whose parameters are views of those vectors, so
+    ``state_dict()`` / ``load_state_dict()`` keep working;
+  * ``_update`` ships the sampled packed transitions to the device and runs pk_dqn_grad -> [allreduce] ->
+    pk_clamp_adam (Double-DQN target, Huber, backward, clamp, Adam: trainer.py:152-195);
+  * with ``torch.distributed`` initialised (one process per GPU), every rank draws the same minibatch, takes its
+    contiguous shard, and the flat gradient is summed with one allreduce BEFORE the clamp.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .agent import AgentTrain, AgentVal
+from .feature_extractor import FeatureExtractor
+from .mlp_model import MLPModel
+from .packed import PK_OBS_BYTES
+from .replay_buffer import ReplayBuffer
+
+DQN_DEFAULT_PARAMS = {  # trainer.py:15-27
+    "epsilon": 0.3,
+    "epsilon_decay": 0.0,
+    "epsilon_min": 0.0,
+    "gamma": 0.95,
+    "batch_size": 32,
+    "first_update_steps": 500,
+    "optimize_per_steps": 1,
+    "target_update": 100,
+    "double_dqn": True,
+    "replay_buffer_size": 100000,
+    "lr": 1e-3,
+}
+
+_PARAM_KEYS_CACHE = {}
+
+
+def _param_keys(n_layers: int):
+    keys = []
+    for i in range(n_layers):
+        keys += [f"layers.{i}.weight", f"layers.{i}.bias"]
+    return keys + ["output.weight", "output.bias"]
+
+
+class FlatAdam:
+    """Adam state of the flat parameter vector, exposing ``state_dict`` / ``load_state_dict`` in
+    torch.optim.Adam's format (per-parameter ``step`` / ``exp_avg`` / ``exp_avg_sq``) so that resume
+    checkpoints interchange with the reference's ``optim.Adam`` (trainer.py:54,84,114)."""
+
+    def __init__(self, model: MLPModel, flat: torch.Tensor, lr: float):
+        self.lr, self.betas, self.eps = float(lr), (0.9, 0.999), 1e-8
+        self.step_count = 0
+        self.exp_avg = torch.zeros_like(flat)
+        self.exp_avg_sq = torch.zeros_like(flat)
+        self._shapes = [tuple(p.shape) for p in model.parameters()]
+
+    def state_dict(self) -> dict:
+        state = {}
+        if self.step_count > 0:
+            off = 0
+            for i, shp in enumerate(self._shapes):
+                n = int(np.prod(shp))
+                state[i] = {"step": torch.tensor(float(self.step_count)),
+                            "exp_avg": self.exp_avg[off:off + n].view(shp).cpu().clone(),
+                            "exp_avg_sq": self.exp_avg_sq[off:off + n].view(shp).cpu().clone()}
+                off += n
+        group = {"lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": 0, "amsgrad": False,
+                 "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                 "decoupled_weight_decay": False, "params": list(range(len(self._shapes)))}
+        return {"state": state, "param_groups": [group]}
+
+    def load_state_dict(self, sd: dict) -> None:
+        g = sd["param_groups"][0]
+        self.lr, self.betas, self.eps = float(g["lr"]), tuple(g["betas"]), float(g["eps"])
+        if g.get("weight_decay", 0) or g.get("amsgrad", False):
+            raise NotImplementedError("weight decay / amsgrad have no kernel (the reference uses neither)")
+        self.exp_avg.zero_()
+        self.exp_avg_sq.zero_()
+        self.step_count = 0
+        off = 0
+        for i, shp in enumerate(self._shapes):
+            n = int(np.prod(shp))
+            st = sd["state"].get(i)
+            if st is not None:
+                self.exp_avg[off:off + n].copy_(st["exp_avg"].reshape(-1))
+                self.exp_avg_sq[off:off + n].copy_(st["exp_avg_sq"].reshape(-1))
+                self.step_count = int(st["step"])
+            off += n
+
+    def zero_grad(self) -> None:  # kept for API familiarity; gradients are overwritten by every update
+        pass
+
+
+class Trainer:
+    def __init__(self, model_params: dict, dqn_params: dict, feature_params: dict, device=None):
+        self.constructor_params = {
+            "model_params": model_params,
+            "dqn_params": dqn_params,
+            "feature_params": feature_params,
+        }
+        if not torch.cuda.is_available():
+            raise RuntimeError("pokeai_b200.Trainer needs a CUDA device (there is no CPU training path)")
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        N.ensure_init(self.device.index if self.device.index is not None else torch.cuda.current_device())
+        self.feature_extractor = FeatureExtractor(**feature_params)
+        self.feature_extractor.device = self.device
+        self.model_params = model_params.copy()
+        self.model_params["input_shape"] = self.feature_extractor.input_shape
+        self.model_params["output_dim"] = self.feature_extractor.output_dim
+        if self.model_params.get("bn", False):
+            raise NotImplementedError("train-mode BatchNorm has no kernel (every recorded run of the reference "
+                                      "uses bn=False); inference with a folded eval-mode BN is supported")
+        # same construction order as the reference (two random inits, then copy): identical torch RNG use
+        self.model, self._flat = self._construct_flat_model()
+        self.target_model, self._flat_target = self._construct_flat_model()
+        self._flat_target.copy_(self._flat)
+        self.total_steps = 0
+        self.total_battles = 0
+        self.update_steps = 0
+        p = DQN_DEFAULT_PARAMS.copy()
+        p.update(dqn_params)
+        self.optimizer = FlatAdam(self.model, self._flat, p["lr"])
+        self.replay_buffer = ReplayBuffer(p["replay_buffer_size"], self.feature_extractor.output_dim)
+        self.epsilon = p["epsilon"]
+        self.epsilon_decay = p["epsilon_decay"]
+        self.epsilon_min = p["epsilon_min"]
+        self.gamma = p["gamma"]
+        self.batch_size = p["batch_size"]
+        self.first_update_steps = p["first_update_steps"]
+        self.optimize_per_steps = p["optimize_per_steps"]
+        self.target_update = p["target_update"]
+        self.double_dqn = p["double_dqn"]
+        self.update_loss_history = []
+
+        m = self.model
+        self._nl, self._H, self._C = m.n_layers, m.n_channels, m.in_channels
+        lib = N.lib()
+        n_prep = lib.pk_mlp_prepared_floats(self._nl, self._H, self._C)
+        self._prepared = torch.zeros(n_prep, dtype=torch.float32, device=self.device)
+        self._prepared_target = torch.zeros(n_prep, dtype=torch.float32, device=self.device)
+        self._grad = torch.zeros_like(self._flat)
+        self._loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._staging = None
+        self._refresh_prepared()
+        self._prepared_target.copy_(self._prepared)
+
+    # -- model plumbing -------------------------------------------------------------------------------
+    def _construct_model(self):
+        return MLPModel(**self.model_params)  # trainer.py:69-71
+
+    def _construct_flat_model(self, flat: Optional[torch.Tensor] = None):
+        """An MLPModel whose parameters are views of one flat fp32 CUDA vector (state_dict order)."""
+        model = self._construct_model()
+        params = list(model.parameters())
+        if flat is None:
+            flat = torch.cat([p.detach().reshape(-1) for p in params]).to(self.device, torch.float32)
+        assert flat.numel() == N.lib().pk_mlp_param_floats(model.n_layers, model.n_channels, model.in_channels)
+        off = 0
+        for p in params:
+            n = p.numel()
+            p.data = flat[off:off + n].view(p.shape)
+            p.requires_grad_(False)
+            off += n
+        return model, flat
+
+    def _refresh_prepared(self) -> None:
+        from . import ops
+        ops.prepare_from_flat(self._flat, self._nl, self._H, self._C, out=self._prepared)
+
+    def _snapshot_model(self) -> MLPModel:
+        """A frozen copy of the online network (get_train_agent / get_val_agent, trainer.py:123-134)."""
+        model, flat = self._construct_flat_model(self._flat.clone())
+        model.eval()
+        model._prepared = self._prepared.clone()
+        model._prepared_key = (str(self.device),) + tuple((p.data_ptr(), p._version) for p in model.parameters())
+        return model
+
+    # -- checkpoints (trainer.py:73-121) ---------------------------------------------------------------
+    @staticmethod
+    def _cpu_sd(model) -> dict:
+        return {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+
+    def save_state(self, resume=False):
+        if resume:
+            return {
+                "model": self._cpu_sd(self.model),
+                "target_model": self._cpu_sd(self.target_model),
+                "optimizer": self.optimizer.state_dict(),
+                "replay_buffer": self.replay_buffer,
+                "constructor_params": self.constructor_params,
+                "total_steps": self.total_steps,
+                "total_battles": self.total_battles,
+                "update_steps": self.update_steps,
+                "update_loss_history": self.update_loss_history,
+            }
+        return {
+            "model": self._cpu_sd(self.model),
+            "constructor_params": self.constructor_params,
+            "update_steps": self.update_steps,
+            "total_battles": self.total_battles,
+        }
+
+    @classmethod
+    def load_state(cls, state, resume=False, **kwargs) -> "Trainer":
+        trainer = cls(**state["constructor_params"], **kwargs)
+        trainer.model.load_state_dict(state["model"])
+        trainer._refresh_prepared()
+        trainer.update_steps = state["update_steps"]
+        if resume:
+            trainer.total_steps = state["total_steps"]
+            trainer.total_battles = state["total_battles"]
+            trainer.target_model.load_state_dict(state["target_model"])
+            from . import ops
+            ops.prepare_from_flat(trainer._flat_target, trainer._nl, trainer._H, trainer._C, out=trainer._prepared_target)
+            trainer.optimizer.load_state_dict(state["optimizer"])
+            trainer.replay_buffer = state["replay_buffer"]
+            trainer.update_loss_history = state["update_loss_history"]
+        return trainer
+
+    def load_initial_model(self, state_dict):
+        self.model.load_state_dict(state_dict)
+        self.target_model.load_state_dict(state_dict)
+        self._refresh_prepared()
+        self._prepared_target.copy_(self._prepared)
+
+    # -- agents (trainer.py:123-134) ----------------------------------------------------------------------
+    def get_train_agent(self):
+        epsilon = max(math.pow(1.0 - self.epsilon_decay, self.total_steps) * self.epsilon, self.epsilon_min)
+        return AgentTrain(self._snapshot_model(), self.feature_extractor, epsilon)
+
+    def get_val_agent(self):
+        return AgentVal(self._snapshot_model(), self.feature_extractor)
+
+    def extend_replay_buffer(self, buffer: ReplayBuffer):
+        steps = len(buffer)
+        self.total_steps += steps
+        self.replay_buffer.extend(buffer.buffer)
+
+    # -- schedule (trainer.py:141-150) ------------------------------------------------------------------------
+    def train(self):
+        while self.update_steps < self.total_steps:
+            update_step = self.update_steps
+            if update_step % self.optimize_per_steps == 0 and update_step >= self.first_update_steps:
+                self._update()
+            if update_step % (self.optimize_per_steps * self.target_update) == 0:
+                self._target_update()
+            self.update_steps += 1
+
+    # -- the update (trainer.py:152-195) ------------------------------------------------------------------------
+    def _ensure_staging(self, n: int) -> None:
+        if self._staging is not None and self._staging["n"] >= n:
+            return
+        # one pinned host block and one device block: [state n*144 | next n*144 | action n*4 | reward n*4 | terminal n]
+        off_next = n * PK_OBS_BYTES
+        off_act = 2 * n * PK_OBS_BYTES
+        off_rew = off_act + 4 * n
+        off_term = off_rew + 4 * n
+        total = (off_term + n + 15) & ~15
+        host = torch.empty(total, dtype=torch.uint8, pin_memory=True)
+        dev = torch.empty(total, dtype=torch.uint8, device=self.device)
+        hn = host.numpy()
+        n_scr = N.lib().pk_dqn_scratch_floats(self._nl, self._H, self._C, n)
+        self._staging = {
+            "n": n, "host": host, "dev": dev, "off": (0, off_next, off_act, off_rew, off_term),
+            "h_state": hn[0:off_next], "h_next": hn[off_next:off_act],
+            "h_action": hn[off_act:off_rew].view(np.int32), "h_reward": hn[off_rew:off_term].view(np.float32),
+            "h_terminal": hn[off_term:off_term + n],
+            "scratch": torch.empty(n_scr, dtype=torch.float32, device=self.device),
+        }
+
+    def _dist(self):
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            return dist
+        return None
+
+    def _update_from_arrays(self, state, next_state, action, reward, terminal, n_global: Optional[int] = None) -> float:
+        """One optimiser step on explicit (already sharded) transition arrays.  Returns the loss
+        (sum of this shard's Huber terms / n_global; the all-reduced mean when distributed)."""
+        n = len(state)
+        n_global = n if n_global is None else n_global
+        self._ensure_staging(max(n, 1))
+        S = self._staging
+        S["h_state"][:n * PK_OBS_BYTES] = np.ascontiguousarray(state).view(np.uint8).reshape(-1)
+        S["h_next"][:n * PK_OBS_BYTES] = np.ascontiguousarray(next_state).view(np.uint8).reshape(-1)
+        S["h_action"][:n] = action
+        S["h_reward"][:n] = reward
+        S["h_terminal"][:n] = terminal
+        S["dev"].copy_(S["host"], non_blocking=True)
+        base = S["dev"].data_ptr()
+        o = S["off"]
+        b = N.pk_batch()
+        b.n, b.n_global = n, n_global
+        b.state, b.next_state = base + o[0], base + o[1]
+        b.action, b.reward, b.terminal = base + o[2], base + o[3], base + o[4]
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        lib = N.lib()
+        if n == 0:  # a rank whose shard of a tiny minibatch is empty still takes part in the allreduce
+            self._grad.zero_()
+            self._loss.zero_()
+        else:
+                N.check(lib.pk_dqn_grad(self._prepared.data_ptr(), self._prepared_target.data_ptr(), self._nl, self._H,
+                                    self.feature_extractor.output_dim, C.byref(b), float(self.gamma),
+                                    1 if self.double_dqn else 0, self._grad.data_ptr(), self._loss.data_ptr(),
+                                    S["scratch"].data_ptr(), stream))
+        dist = self._dist()
+        if dist is not None:  # sum of shard gradients == gradient of the global mean loss; clamp comes after
+            dist.all_reduce(self._grad)
+            dist.all_reduce(self._loss)
+        opt = self.optimizer
+        opt.step_count += 1
+        N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
+                                  opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
+                                  opt.betas[1], opt.eps, opt.step_count, self._prepared.data_ptr(), stream))
+        return float(self._loss.item())
+
+    def _update(self):
+        idx = self.replay_buffer.sample_indices(self.batch_size)
+        state, next_state, action, reward, terminal = self.replay_buffer.gather(idx)
+        if bool(terminal.all()):
+            # the reference fails here too: np.stack([]) at trainer.py:157
+            raise ValueError("need at least one array to stack")
+        n_global = len(idx)
+        dist = self._dist()
+        if dist is not None:  # every rank drew the same minibatch (same `random` state); keep a contiguous shard
+            w, r = dist.get_world_size(), dist.get_rank()
+            lo, hi = (n_global * r) // w, (n_global * (r + 1)) // w
+            state, next_state, action, reward, terminal = (x[lo:hi] for x in (state, next_state, action, reward, terminal))
+        loss = self._update_from_arrays(state, next_state, action, reward, terminal, n_global)
+        self.update_loss_history.append(loss)
+
+    def _target_update(self):  # trainer.py:197-198
+        self._flat_target.copy_(self._flat)
+        self._prepared_target.copy_(self._prepared)
