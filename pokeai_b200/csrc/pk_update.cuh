@@ -315,7 +315,12 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
   for (int l = 1; l < NL; ++l)
 #pragma unroll
     for (int i = 0; i < EPT; ++i) out[lay.wl[l] + own_k * HP + own_j0 + i] = acc_w[l - 1][i];
-  if (tid < 4) out[lay.bout + tid] = tid == 0 ? acc_bout : tid == 1 ? acc_loss : 0.f;
+  if (tid == 0) {  // bout[0] = d/d(output bias), bout[1] = this CTA's share of the loss
+    out[lay.bout + 0] = acc_bout;
+    out[lay.bout + 1] = acc_loss;
+    out[lay.bout + 2] = 0.f;
+    out[lay.bout + 3] = 0.f;
+  }
 }
 
 // gsum[p] (+)= sum over CTAs of partial[cta][p], in CTA order (deterministic)

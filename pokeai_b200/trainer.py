@@ -278,10 +278,8 @@ class Trainer:
         }
 
     def _dist(self):
-        import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            return dist
-        return None
+        from .dist import active_group
+        return active_group()
 
     def _update_from_arrays(self, state, next_state, action, reward, terminal, n_global: Optional[int] = None) -> float:
         """One optimiser step on explicit (already sharded) transition arrays.  Returns the loss
@@ -314,8 +312,8 @@ class Trainer:
                                     S["scratch"].data_ptr(), stream))
         dist = self._dist()
         if dist is not None:  # sum of shard gradients == gradient of the global mean loss; clamp comes after
-            dist.all_reduce(self._grad)
-            dist.all_reduce(self._loss)
+            from .dist import allreduce_sum_
+            allreduce_sum_(self._grad, self._loss, dist)
         opt = self.optimizer
         opt.step_count += 1
         N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
@@ -332,8 +330,8 @@ class Trainer:
         n_global = len(idx)
         dist = self._dist()
         if dist is not None:  # every rank drew the same minibatch (same `random` state); keep a contiguous shard
-            w, r = dist.get_world_size(), dist.get_rank()
-            lo, hi = (n_global * r) // w, (n_global * (r + 1)) // w
+            from .dist import shard_bounds
+            lo, hi = shard_bounds(n_global, dist.get_world_size(), dist.get_rank())
             state, next_state, action, reward, terminal = (x[lo:hi] for x in (state, next_state, action, reward, terminal))
         loss = self._update_from_arrays(state, next_state, action, reward, terminal, n_global)
         self.update_loss_history.append(loss)
