@@ -138,6 +138,9 @@ PK_API const char* pk_last_error(void);
 PK_API int pk_init(const pk_tables* tables, int device);
 /* Number of feature channels C = 50 + 2 + n_species + n_moves + n_items (617). */
 PK_API int pk_n_channels(void);
+/* Debugging aid: when non-NULL, pk_encode / pk_decide record %globaltimer (ns) of lane 0 at 10 phase points of
+ * the first battle of every warp into device_buffer[(cta * warps + warp) * 16 + phase].  NULL switches it off. */
+PK_API int pk_debug_set_trace(unsigned long long* device_buffer);
 /* Number of SMs of the initialised device (grid sizing information for callers). */
 PK_API int pk_sm_count(void);
 

@@ -162,6 +162,7 @@ struct PkSelect {
   const float* u_explore;
   const float* u_pick;
   float* probs;
+  unsigned long long* trace;  // debug phase trace, normally null
 };
 
 // ---- small PTX helpers -----------------------------------------------------------------------

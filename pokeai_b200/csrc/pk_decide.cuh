@@ -294,6 +294,33 @@ __device__ __forceinline__ void pk_hidden_layer(const float* __restrict__ WT, co
     for (int i = 0; i < CPL; ++i) h[c][i] = fmaxf(acc[c][i], 0.0f);
 }
 
+// register-lean variant: the layer input is already in hbuf (AT columns x HP); returns the pre-activation in acc
+template <int CPL, int AT>
+__device__ __forceinline__ void pk_hidden_from_smem(const float* __restrict__ WT, const float* __restrict__ bias,
+                                                    const float* hbuf, float (&acc)[AT][CPL], int lane) {
+  constexpr int HP = 32 * CPL;
+  {
+    float bv[CPL];
+    pk_lds_vec<CPL>(bias, lane, bv);
+#pragma unroll
+    for (int c = 0; c < AT; ++c)
+#pragma unroll
+      for (int i = 0; i < CPL; ++i) acc[c][i] = bv[i];
+  }
+#pragma unroll 2
+  for (int k = 0; k < HP; k += 2) {
+    float w0[CPL], w1[CPL];
+    pk_lds_vec<CPL>(WT + k * HP, lane, w0);
+    pk_lds_vec<CPL>(WT + (k + 1) * HP, lane, w1);
+#pragma unroll
+    for (int c = 0; c < AT; ++c) {
+      const float2 hv = *reinterpret_cast<const float2*>(hbuf + c * HP + k);
+      pk_fma_vec<CPL>(acc[c], w0, hv.x);
+      pk_fma_vec<CPL>(acc[c], w1, hv.y);
+    }
+  }
+}
+
 // hidden layers 1..n_layers-1 and the 1-channel head; h holds relu(layer 0) on entry, qv on exit is
 // the Q value of every column in every lane
 template <int CPL, int AT>
@@ -383,8 +410,18 @@ __device__ __forceinline__ void pk_poke_feature_block(float* __restrict__ g, con
   }
 }
 
-template <int CPL, int A>
-__global__ void __launch_bounds__(512, 1)
+// optional phase trace (debugging / DESIGN.md timeline): globaltimer of lane 0 at up to 16 points of the FIRST
+// battle of every warp; sel.trace == nullptr in normal operation
+__device__ __forceinline__ void pk_trace(unsigned long long* tr, int slot, int phase) {
+  if (tr != nullptr && (threadIdx.x & 31) == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    tr[(size_t)slot * 16 + phase] = t;
+  }
+}
+
+template <int CPL, int A, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
 pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restrict__ prep, PkLayout lay,
                  float* __restrict__ feat, int* __restrict__ mask, float* __restrict__ q,
                  int* __restrict__ action, PkSelect sel, int zero_by_tma) {
@@ -394,9 +431,12 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const bool with_mlp = prep != nullptr;
   const int L = lay.C * A;  // floats per battle
-  const bool use_tma = feat != nullptr && zero_by_tma != 0;
+  const bool use_tma = feat != nullptr && (zero_by_tma & 1) != 0;
   const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp, use_tma);
 
+  unsigned long long* tr = sel.trace;
+  const int tslot = blockIdx.x * nwarps + warp;
+  pk_trace(tr, tslot, 0);
   if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
   const float* zero_tile = nullptr;
   if (use_tma) {
@@ -406,6 +446,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
     zero_tile = reinterpret_cast<const float*>(z);
   }
   if (with_mlp || use_tma) __syncthreads();
+  pk_trace(tr, tslot, 1);
 
   unsigned char* wa = smem + plan.warp_area + warp * plan.warp_stride;
   uint4* rec = reinterpret_cast<uint4*>(wa);
@@ -431,6 +472,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
     if (lane < 9) rec[lane] = cur;
     if (b + stride < B && lane < 9) cur = __ldg(packed + (b + stride) * 9 + lane);  // prefetch, consumed next turn
     __syncwarp();
+    pk_trace(tr, tslot, 2);
     const int n_act = min((int)r[PK_OFF_NACT], A);
     if (mask != nullptr && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;  // feature_extractor.py:50-51
     sv[lane] = pk_state_feature(r, lane);
@@ -445,6 +487,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
       }
     }
     __syncwarp();
+    pk_trace(tr, tslot, 3);
 
     float* gfeat = feat != nullptr ? feat + (size_t)b * L : nullptr;
     if (gfeat != nullptr) {
@@ -458,59 +501,127 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
         pk_poke_feature_block<A>(gfeat, idx, zero_row, lane);
       }
     }
-    if (!with_mlp) continue;
+    pk_trace(tr, tslot, 4);
+    if (!with_mlp) {
+      tr = nullptr;
+      continue;
+    }
 
-    // ---- layer 0, state part: shared by every column of this battle ------------------------------
-    float base[CPL];
+    // ---- layer 0, state part: shared by every column of this battle (two chains for ILP) ----------
+    float base[CPL], base2[CPL];
 #pragma unroll
-    for (int i = 0; i < CPL; ++i) base[i] = b1r[i];
-#pragma unroll 1
-    for (int k4 = 0; k4 < 52; k4 += 4) {
+    for (int i = 0; i < CPL; ++i) {
+      base[i] = b1r[i];
+      base2[i] = 0.0f;
+    }
+#pragma unroll 3
+    for (int k4 = 0; k4 < 48; k4 += 4) {  // dense and branch-free: 0 * w adds nothing, and no compare/branch per row
       const float4 s4 = *reinterpret_cast<const float4*>(sv + k4);
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk) {
         const float x = kk == 0 ? s4.x : kk == 1 ? s4.y : kk == 2 ? s4.z : s4.w;
-        if (x != 0.0f) {  // warp-uniform; k >= 50 reads zeros
-          float w[CPL];
-          pk_lds_vec<CPL>(s_w1s + (k4 + kk) * HP, lane, w);
-          pk_fma_vec<CPL>(base, w, x);
-        }
+        float w[CPL];
+        pk_lds_vec<CPL>(s_w1s + (k4 + kk) * HP, lane, w);
+        if (kk & 1) pk_fma_vec<CPL>(base2, w, x);
+        else pk_fma_vec<CPL>(base, w, x);
       }
     }
-    // ---- layer 0, choice part: <= 8 one-hot rows per column, gathered from W1^T -------------------
-    float h[AT][CPL];
+    {
+      const float2 s2 = *reinterpret_cast<const float2*>(sv + 48);  // rows 48, 49
+      float w[CPL];
+      pk_lds_vec<CPL>(s_w1s + 48 * HP, lane, w);
+      pk_fma_vec<CPL>(base, w, s2.x);
+      pk_lds_vec<CPL>(s_w1s + 49 * HP, lane, w);
+      pk_fma_vec<CPL>(base2, w, s2.y);
+    }
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) base[i] += base2[i];
+    pk_trace(tr, tslot, 5);
+    // ---- layer 0, choice part: 8 row slots per column gathered from W1^T (absent slots and illegal columns
+    //      point at the all-zero row, so there is no branch); the loads of column c+1 are in flight while
+    //      column c is summed; relu(h) goes straight to the warp's hbuf --------------------------------------
+    float gc[8][CPL], gn[8][CPL];
+    {
+      const int4 ia = *reinterpret_cast<const int4*>(idx);
+      const int4 ib = *reinterpret_cast<const int4*>(idx + 4);
+      pk_ldg_vec<CPL>(w1t + (size_t)ia.x * HP, lane, gc[0]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ia.y * HP, lane, gc[1]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ia.z * HP, lane, gc[2]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ia.w * HP, lane, gc[3]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ib.x * HP, lane, gc[4]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ib.y * HP, lane, gc[5]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ib.z * HP, lane, gc[6]);
+      pk_ldg_vec<CPL>(w1t + (size_t)ib.w * HP, lane, gc[7]);
+    }
 #pragma unroll
     for (int c = 0; c < AT; ++c) {
-#pragma unroll
-      for (int i = 0; i < CPL; ++i) h[c][i] = base[i];
-      if (c < n_act) {  // warp-uniform
-        const int4 ia = *reinterpret_cast<const int4*>(idx + 8 * c);
-        const int4 ib = *reinterpret_cast<const int4*>(idx + 8 * c + 4);
-        float g0[CPL], g1[CPL], g2[CPL];
-        pk_ldg_vec<CPL>(w1t + (size_t)ia.z * HP, lane, g0);  // species
-        pk_ldg_vec<CPL>(w1t + (size_t)ia.w * HP, lane, g1);  // item
-        pk_ldg_vec<CPL>(w1t + (size_t)ib.x * HP, lane, g2);  // first move
-        // any of: switch / force flags, further moves (a switch target's move list)
-        const bool more = min(min(ia.x, ia.y), min(ib.y, min(ib.z, ib.w))) != zero_row;  // valid rows are < zero_row
-        if (more) {
-          float g3[CPL], g4[CPL], g5[CPL], g6[CPL], g7[CPL];
-          pk_ldg_vec<CPL>(w1t + (size_t)ia.x * HP, lane, g3);
-          pk_ldg_vec<CPL>(w1t + (size_t)ia.y * HP, lane, g4);
-          pk_ldg_vec<CPL>(w1t + (size_t)ib.y * HP, lane, g5);
-          pk_ldg_vec<CPL>(w1t + (size_t)ib.z * HP, lane, g6);
-          pk_ldg_vec<CPL>(w1t + (size_t)ib.w * HP, lane, g7);
-#pragma unroll
-          for (int i = 0; i < CPL; ++i) h[c][i] = ((((h[c][i] + g3[i]) + g4[i]) + g5[i]) + g6[i]) + g7[i];
-        }
-#pragma unroll
-        for (int i = 0; i < CPL; ++i) h[c][i] = ((h[c][i] + g0[i]) + g1[i]) + g2[i];
+      if (c + 1 < AT) {
+        const int4 ia = *reinterpret_cast<const int4*>(idx + 8 * (c + 1));
+        const int4 ib = *reinterpret_cast<const int4*>(idx + 8 * (c + 1) + 4);
+        pk_ldg_vec<CPL>(w1t + (size_t)ia.x * HP, lane, gn[0]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ia.y * HP, lane, gn[1]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ia.z * HP, lane, gn[2]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ia.w * HP, lane, gn[3]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ib.x * HP, lane, gn[4]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ib.y * HP, lane, gn[5]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ib.z * HP, lane, gn[6]);
+        pk_ldg_vec<CPL>(w1t + (size_t)ib.w * HP, lane, gn[7]);
       }
+      float hc[CPL];
 #pragma unroll
-      for (int i = 0; i < CPL; ++i) h[c][i] = fmaxf(h[c][i], 0.0f);
+      for (int i = 0; i < CPL; ++i) {
+        const float s01 = gc[0][i] + gc[1][i], s23 = gc[2][i] + gc[3][i];
+        const float s45 = gc[4][i] + gc[5][i], s67 = gc[6][i] + gc[7][i];
+        hc[i] = fmaxf(base[i] + ((s01 + s23) + (s45 + s67)), 0.0f);
+      }
+      pk_sts_vec<CPL>(hbuf + c * HP, lane, hc);
+      if (c + 1 < AT) {
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+#pragma unroll
+          for (int i = 0; i < CPL; ++i) gc[t][i] = gn[t][i];
+      }
     }
-    // ---- hidden layers + head -----------------------------------------------------------------------
+    __syncwarp();
+    pk_trace(tr, tslot, 6);
+    // ---- hidden layers (input in hbuf) + head ----------------------------------------------------------
     float qv[AT];
-    pk_mlp_tail<CPL, AT>(s_tail, lay, hbuf, h, qv, lane);
+    {
+      const unsigned tb = lay.b[0];
+      float acc[AT][CPL];
+      for (int l = 1; l < lay.n_layers; ++l) {
+        pk_hidden_from_smem<CPL, AT>(s_tail + (lay.wl[l] - tb), s_tail + (lay.b[l] - tb), hbuf, acc, lane);
+        if (l + 1 < lay.n_layers) {  // feed the next hidden layer through hbuf
+          __syncwarp();
+#pragma unroll
+          for (int c = 0; c < AT; ++c) {
+            float hc[CPL];
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) hc[i] = fmaxf(acc[c][i], 0.0f);
+            pk_sts_vec<CPL>(hbuf + c * HP, lane, hc);
+          }
+          __syncwarp();
+        }
+      }
+      if (lay.n_layers == 1) {  // single layer: the head reads relu(layer 0) back from hbuf
+#pragma unroll
+        for (int c = 0; c < AT; ++c) pk_lds_vec<CPL>(hbuf + c * HP, lane, acc[c]);
+      }
+      float wo[CPL];
+      pk_lds_vec<CPL>(s_tail + (lay.wout - tb), lane, wo);
+      const float bo = s_tail[lay.bout - tb];
+#pragma unroll
+      for (int c = 0; c < AT; ++c) {
+        float p = 0.0f;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) p = fmaf(wo[i], fmaxf(acc[c][i], 0.0f), p);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
+        qv[c] = p + bo;
+      }
+    }
+    __syncwarp();  // hbuf is rewritten by the next battle
+    pk_trace(tr, tslot, 7);
     float myq = 0.0f;
 #pragma unroll
     for (int c = 0; c < AT; ++c)
@@ -520,11 +631,14 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
       const int act = pk_select_dev<AT>(qv, (1u << n_act) - 1u, A, sel, b, lane == 0);
       if (lane == 0) action[b] = act;
     }
+    pk_trace(tr, tslot, 8);
     if (gfeat != nullptr && use_tma) {  // the zeros have landed by now; finish the block
       if (lane == 0) pk_bulk_wait_all();
       __syncwarp();
       pk_poke_feature_block<A>(gfeat, idx, zero_row, lane);
     }
+    pk_trace(tr, tslot, 9);
+    tr = nullptr;  // first battle of the warp only
   }
 }
 

@@ -45,6 +45,7 @@ struct PkGlobal {
   int encode_warps = 16;
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
+  unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
 };
 static PkGlobal g;
 
@@ -83,7 +84,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.device = device;
   g.sm_count = prop.multiProcessorCount;
   g.max_smem = (int)prop.sharedMemPerBlockOptin;
-  g.decide_warps = env_int("PK_DECIDE_WARPS", 16, 1, 16);
+  g.decide_warps = env_int("PK_DECIDE_WARPS", 16, 1, 32);
   g.encode_warps = env_int("PK_ENCODE_WARPS", 16, 1, 16);
   g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
@@ -95,6 +96,10 @@ extern "C" int pk_init(const pk_tables* t, int device) {
     if (g.device < 0) return pk_fail(PK_ERR_NOT_INIT, "pk_init has not been called"); \
   } while (0)
 
+extern "C" int pk_debug_set_trace(unsigned long long* device_buffer) {
+  g.trace = device_buffer;
+  return PK_OK;
+}
 extern "C" int pk_n_channels(void) { return g.device < 0 ? 0 : g.tab.C; }
 extern "C" int pk_sm_count(void) { return g.device < 0 ? 0 : g.sm_count; }
 
@@ -176,6 +181,7 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   PkSelect ps;
   memset(&ps, 0, sizeof(ps));
   ps.temperature = 1.0f;
+  ps.trace = g.trace;
   if (with_mlp) {
     PK_REQUIRE(n_layers >= 1 && n_layers <= PK_MAX_LAYERS && n_channels >= 1, "bad network shape %d x %d", n_layers,
                n_channels);
@@ -202,6 +208,7 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   const int CPL = lay.HP / 32;
   const bool use_tma = feat != nullptr && g.zero_by_tma != 0;
   int nwarps = with_mlp ? g.decide_warps : g.encode_warps;
+  if (CPL > 2 && nwarps > 16) nwarps = 16;  // the 128-channel instantiation needs > 64 registers per thread
   PkSmemPlan plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma);
   while (plan.total > (unsigned)g.max_smem && nwarps > 1) {  // drop warps until the plan fits
     --nwarps;
@@ -216,10 +223,17 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   const uint4* pk = reinterpret_cast<const uint4*>(packed);
 #define PK_LAUNCH_DECIDE(C_, A_)                                                                              \
   {                                                                                                           \
-    int rc_ = pk_set_smem(pk_decide_kernel<C_, A_>, plan.total);                                              \
-    if (rc_) return rc_;                                                                                      \
-    pk_decide_kernel<C_, A_><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask, q,      \
-                                                                    action, ps, use_tma ? 1 : 0);             \
+    if (nwarps > 16) {                                                                                        \
+      int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, (C_ <= 2 ? 1024 : 512)>, plan.total);                    \
+      if (rc_) return rc_;                                                                                    \
+      pk_decide_kernel<C_, A_, (C_ <= 2 ? 1024 : 512)><<<grid, nwarps * 32, plan.total, st>>>(                \
+          pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0);                                  \
+    } else {                                                                                                  \
+      int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                       \
+      if (rc_) return rc_;                                                                                    \
+      pk_decide_kernel<C_, A_, 512><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask,  \
+                                                                           q, action, ps, use_tma ? 1 : 0);   \
+    }                                                                                                         \
   }
 #define PK_LAUNCH_DECIDE_A(C_)                                        \
   switch (A) {                                                        \
