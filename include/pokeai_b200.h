@@ -141,6 +141,11 @@ PK_API int pk_n_channels(void);
 /* Debugging aid: when non-NULL, pk_encode / pk_decide record %globaltimer (ns) of lane 0 at 10 phase points of
  * the first battle of every warp into device_buffer[(cta * warps + warp) * 16 + phase].  NULL switches it off. */
 PK_API int pk_debug_set_trace(unsigned long long* device_buffer);
+/* Tuning / test aid: which pk_decide kernel runs for networks of <= 64 channels.  0 = one battle per warp,
+ * 2 = two battles per warp (one per half-warp in the MLP), 1 (default) = paired only when features are not
+ * materialised (the measured optimum, profiles/r01_pair_vs_single.txt).  Results are identical up to fp32
+ * summation order. */
+PK_API int pk_debug_set_pairing(int mode);
 /* Number of SMs of the initialised device (grid sizing information for callers). */
 PK_API int pk_sm_count(void);
 

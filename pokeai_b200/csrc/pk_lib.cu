@@ -9,7 +9,7 @@
 #include <cstring>
 
 #include "pk_common.cuh"
-#include "pk_decide.cuh"
+#include "pk_decide2.cuh"
 #include "pk_update.cuh"
 
 // ---- error handling -----------------------------------------------------------------------------
@@ -43,6 +43,7 @@ struct PkGlobal {
   // tuning knobs (environment: PK_DECIDE_WARPS / PK_ENCODE_WARPS / PK_CTAS_PER_SM / PK_ZERO_TMA)
   int decide_warps = 16;
   int encode_warps = 16;
+  int decide_pair = 1;
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
@@ -88,6 +89,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.encode_warps = env_int("PK_ENCODE_WARPS", 16, 1, 16);
   g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
+  g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   return PK_OK;
 }
 
@@ -98,6 +100,11 @@ extern "C" int pk_init(const pk_tables* t, int device) {
 
 extern "C" int pk_debug_set_trace(unsigned long long* device_buffer) {
   g.trace = device_buffer;
+  return PK_OK;
+}
+extern "C" int pk_debug_set_pairing(int mode) {
+  if (mode < 0 || mode > 2) return pk_fail(PK_ERR_INVALID, "pk_debug_set_pairing: mode %d not in 0..2", mode);
+  g.decide_pair = mode;
   return PK_OK;
 }
 extern "C" int pk_n_channels(void) { return g.device < 0 ? 0 : g.tab.C; }
@@ -207,8 +214,47 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   }
   const int CPL = lay.HP / 32;
   const bool use_tma = feat != nullptr && g.zero_by_tma != 0;
+  const uint4* pk = reinterpret_cast<const uint4*>(packed);
+  // measured (profiles/r01_pair_vs_single.txt): pairing wins when the features are not materialised (305 vs 275 M
+  // decisions/s at 65 536 states) and loses when they are (two 22 KB blocks per warp back-pressure the store path)
+  if (with_mlp && lay.HP <= 64 && (g.decide_pair == 2 || (g.decide_pair == 1 && feat == nullptr))) {
+    // paired kernel (pk_decide2.cuh): a warp takes two battles, one per half-warp in the MLP
+    int nw = g.decide_warps > 16 ? 16 : g.decide_warps;
+    PkSmemPlan plan2 = pk2_smem_plan(lay, A, nw, use_tma);
+    while (plan2.total > (unsigned)g.max_smem && nw > 1) plan2 = pk2_smem_plan(lay, A, --nw, use_tma);
+    if (plan2.total <= (unsigned)g.max_smem) {
+      const long long NP = ((long long)B + 1) / 2;
+      int grid2 = (int)((NP + nw - 1) / nw);
+      if (grid2 > g.sm_count * g.ctas_per_sm) grid2 = g.sm_count * g.ctas_per_sm;
+#define PK_LAUNCH_PAIR(CH_, A_)                                                                           \
+  {                                                                                                       \
+    int rc_ = pk_set_smem(pk_decide2_kernel<CH_, A_>, plan2.total);                                       \
+    if (rc_) return rc_;                                                                                  \
+    pk_decide2_kernel<CH_, A_><<<grid2, nw * 32, plan2.total, st>>>(pk, B, prepared, lay, feat, mask, q,  \
+                                                                    action, ps, use_tma ? 1 : 0);         \
+  }
+#define PK_LAUNCH_PAIR_A(CH_)                                       \
+  switch (A) {                                                      \
+    case 1: PK_LAUNCH_PAIR(CH_, 1) break;                           \
+    case 2: PK_LAUNCH_PAIR(CH_, 2) break;                           \
+    case 3: PK_LAUNCH_PAIR(CH_, 3) break;                           \
+    case 4: PK_LAUNCH_PAIR(CH_, 4) break;                           \
+    case 5: PK_LAUNCH_PAIR(CH_, 5) break;                           \
+    case 6: PK_LAUNCH_PAIR(CH_, 6) break;                           \
+    case 7: PK_LAUNCH_PAIR(CH_, 7) break;                           \
+    case 8: PK_LAUNCH_PAIR(CH_, 8) break;                           \
+    default: PK_LAUNCH_PAIR(CH_, 9) break;                          \
+  }
+      if (lay.HP == 32) { PK_LAUNCH_PAIR_A(2) }
+      else { PK_LAUNCH_PAIR_A(4) }
+#undef PK_LAUNCH_PAIR_A
+#undef PK_LAUNCH_PAIR
+      PK_CUDA(cudaGetLastError());
+      return PK_OK;
+    }
+  }
   int nwarps = with_mlp ? g.decide_warps : g.encode_warps;
-  if (CPL > 2 && nwarps > 16) nwarps = 16;  // the 128-channel instantiation needs > 64 registers per thread
+  if (nwarps > 16) nwarps = 16;  // the 128-channel instantiation needs > 64 registers per thread
   PkSmemPlan plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma);
   while (plan.total > (unsigned)g.max_smem && nwarps > 1) {  // drop warps until the plan fits
     --nwarps;
@@ -220,20 +266,12 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
                    n_layers, n_channels, plan.total, g.max_smem);
   int grid = (B + nwarps - 1) / nwarps;
   if (grid > g.sm_count * g.ctas_per_sm) grid = g.sm_count * g.ctas_per_sm;
-  const uint4* pk = reinterpret_cast<const uint4*>(packed);
 #define PK_LAUNCH_DECIDE(C_, A_)                                                                              \
   {                                                                                                           \
-    if (nwarps > 16) {                                                                                        \
-      int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, (C_ <= 2 ? 1024 : 512)>, plan.total);                    \
-      if (rc_) return rc_;                                                                                    \
-      pk_decide_kernel<C_, A_, (C_ <= 2 ? 1024 : 512)><<<grid, nwarps * 32, plan.total, st>>>(                \
-          pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0);                                  \
-    } else {                                                                                                  \
-      int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                       \
-      if (rc_) return rc_;                                                                                    \
-      pk_decide_kernel<C_, A_, 512><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask,  \
-                                                                           q, action, ps, use_tma ? 1 : 0);   \
-    }                                                                                                         \
+    int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                         \
+    if (rc_) return rc_;                                                                                      \
+    pk_decide_kernel<C_, A_, 512><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask,    \
+                                                                         q, action, ps, use_tma ? 1 : 0);     \
   }
 #define PK_LAUNCH_DECIDE_A(C_)                                        \
   switch (A) {                                                        \

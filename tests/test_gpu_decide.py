@@ -178,6 +178,35 @@ def test_decide_matches_oracle(tables, dev, ps, nl, H, B, kind):
     np.testing.assert_allclose(q2.cpu().numpy(), qo, rtol=Q_RTOL, atol=Q_ATOL)
 
 
+@pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 64, 4097), (6, 2, 64, 1), (3, 3, 24, 301), (4, 1, 64, 77), (6, 4, 64, 500)])
+def test_paired_and_single_kernels_agree_with_oracle(tables, dev, ps, nl, H, B):
+    """pk_decide has two kernels for <= 64 channels (one battle per warp / two per warp, pk_decide2.cuh); both must
+    give bit-exact features and masks and Q within tolerance, with and without materialised features, odd B included"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import _native as N, ops
+    from pokeai_b200.packed import synth_packed
+    A = 4 + ps - 1
+    rec = synth_packed(B, seed=B + H, party_size=ps, kind="ragged", tables=tables)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=H * nl)
+    fo, mo = packed_oracle.encode(rec, ps, tables)
+    with torch.no_grad():
+        qo = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    prepared, _, _, _ = ops.prepare_weights(sd, dev)
+    try:
+        for mode in (0, 2):
+            N.check(N.lib().pk_debug_set_pairing(mode))
+            for mat in (True, False):
+                f, m, q, a = ops.decide(_to_dev(rec, dev), A, prepared, nl, H, materialise=mat)
+                qg = q.cpu().numpy()
+                np.testing.assert_allclose(qg, qo, rtol=Q_RTOL, atol=Q_ATOL, err_msg=f"pairing={mode} mat={mat}")
+                assert np.array_equal(m.cpu().numpy(), mo)
+                assert np.array_equal(a.cpu().numpy(), ref_port.masked_argmax(qg, mo))
+                if mat:
+                    assert np.array_equal(bits(f.cpu().numpy()), bits(fo)), f"pairing={mode}"
+    finally:
+        N.check(N.lib().pk_debug_set_pairing(1))
+
+
 def test_dense_forward_on_arbitrary_dense_input(tables, dev):
     """_calc_q_vector_batch accepts any float tensor, not only one-hot features"""
     from oracle import ref_port
