@@ -234,6 +234,27 @@ PK_API int pk_session_fetch(pk_session* s, int B, float* feat_host, int32_t* mas
 PK_API const float* pk_session_features(const pk_session* s);
 PK_API const int32_t* pk_session_mask(const pk_session* s);
 
+/* ---- wide network: the tensor-core path (BASELINE configs[4], 4 x 2048) -------------------------------
+ * Same MLPModel (mlp_model.py:5-30) evaluated as bf16 x bf16 -> fp32 tcgen05 GEMMs with fused bias + ReLU.
+ * n_channels must be a multiple of 256.  Tolerance: bf16 operands, fp32 accumulation (|dq| <= 2e-2 on O(1)
+ * logits against the fp32 reference). */
+/* Y (M,N) = act(A (M,K) . W (N,K)^T + bias): A, W bf16 row-major with K contiguous (W is exactly a state_dict
+ * weight cast to bf16); out_bf16 and/or out_f32 row-major; K % 64 == 0, N % 256 == 0; relu != 0 applies max(.,0). */
+PK_API int pk_gemm_bf16(const void* a_bf16, const void* w_bf16, const float* bias, void* out_bf16, float* out_f32,
+                        int M, int N, int K, int relu, void* stream);
+/* Bytes of the prepared wide network (bf16 weights, K of layer 0 padded 617 -> 640; fp32 biases and head); 0 if the
+ * shape is unsupported. */
+PK_API size_t pk_wide_prepared_bytes(int n_layers, int n_channels, int in_channels);
+PK_API int pk_wide_prepare(const pk_mlp* m, void* wide_prepared, void* stream);
+/* Bytes of caller-owned scratch for pk_wide_forward at batch B: the bf16 operand X (B*A, 640) and two
+ * (B*A, n_channels) bf16 activation buffers. */
+PK_API size_t pk_wide_workspace_bytes(int n_layers, int n_channels, int in_channels, int B, int A);
+/* transform + forward + select for the wide network (agent_val.py:8-11 with a 4 x 2048 MLPModel): mask (B,A) int32 or
+ * NULL, q (B,A) fp32, action (B,) int32 or NULL (needs mask). */
+PK_API int pk_wide_forward(const pk_obs* packed, int B, int A, const void* wide_prepared, int n_layers, int n_channels,
+                           void* workspace, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

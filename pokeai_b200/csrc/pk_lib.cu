@@ -11,6 +11,7 @@
 #include "pk_common.cuh"
 #include "pk_decide2.cuh"
 #include "pk_update.cuh"
+#include "pk_wide.cuh"
 
 // ---- error handling -----------------------------------------------------------------------------
 static thread_local char g_err[512] = "";
@@ -542,3 +543,4 @@ extern "C" int pk_session_encode_host(pk_session* s, const pk_obs* packed_host, 
 
 extern "C" const float* pk_session_features(const pk_session* s) { return s ? s->d_feat : nullptr; }
 extern "C" const int32_t* pk_session_mask(const pk_session* s) { return s ? s->d_mask : nullptr; }
+#include "pk_wide_api.inc"

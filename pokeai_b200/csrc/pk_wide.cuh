@@ -1,0 +1,362 @@
+// Wide policy network (BASELINE.json configs[4]: 4 x 2048 hidden) -- the tensor-core path.
+//
+// The reference evaluates the same MLPModel (mlp_model.py:5-30) whatever its width; at 2048 channels the
+// per-column MLP is a chain of dense contractions (36 864 rows x 2048 x 2048 at 4 096 battles), 11 000 FLOP/B,
+// so it belongs on the 5th-generation tensor cores:
+//
+//   pk_wide_encode_kernel   packed records -> X (B*A, 640) bf16, K-major rows (one row per action column: the
+//                           50 state values, the <= 8 ones, zero padding 617 -> 640); the dense feature tensor of
+//                           the reference is never built
+//   pk_wide_gemm_kernel     Y = act(X W^T + b): TMA (cp.async.bulk.tensor, SWIZZLE_128B) fills a 4-stage shared-memory
+//                           ring, ONE elected thread issues tcgen05.mma (cta_group::1, kind::f16, bf16 x bf16 ->
+//                           fp32) into a double-buffered TMEM accumulator (2 x 256 columns), four epilogue warps
+//                           read it back with tcgen05.ld, add the bias, apply ReLU and store bf16 (or fp32) rows.
+//                           Persistent: one CTA per SM walks the (m, n) tiles; the 8 n-tiles of one m-block are
+//                           adjacent in the walk so the activation block is read from HBM once.
+//   pk_wide_head_kernel     q = h . w_out + b_out per row, then the masked selection of pk_decide.cuh
+//
+// Numerics: operands are rounded to bf16, accumulation is fp32 -- the bf16 tolerance of SURVEY.md 8c
+// (|dq| <= 2e-2 on O(1) logits) applies, not the 1e-5 of the fp32 small-net path.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "pk_decide.cuh"
+
+#define PKW_BM 128
+#define PKW_BN 256
+#define PKW_BK 64
+#define PKW_STAGES 4
+#define PKW_KPAD0 640  // 617 input channels padded to a multiple of PKW_BK
+#define PKW_THREADS 192
+#define PKW_A_BYTES (PKW_BM * PKW_BK * 2)
+#define PKW_B_BYTES (PKW_BN * PKW_BK * 2)
+#define PKW_STAGE_BYTES (PKW_A_BYTES + PKW_B_BYTES)
+#define PKW_SMEM_BYTES (PKW_STAGES * PKW_STAGE_BYTES + 1024 + 256)
+
+// ---- PTX wrappers --------------------------------------------------------------------------------------
+__device__ __forceinline__ void pkw_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(pk_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void pkw_tma_load_2d(void* sdst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          pk_smem_u32(sdst)),
+      "l"(map), "r"(pk_smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void pkw_prefetch_map(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void pkw_tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void pkw_tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void pkw_tmem_alloc(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(pk_smem_u32(slot)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void pkw_tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; issued by one thread for the whole CTA
+__device__ __forceinline__ void pkw_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// arrives on the mbarrier once every MMA issued so far by this thread has completed (implies fence::before_thread_sync)
+__device__ __forceinline__ void pkw_mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(pk_smem_u32(bar))
+               : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread t of the warp gets TMEM lane (base lane + t)
+__device__ __forceinline__ void pkw_tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void pkw_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor)
+__device__ __forceinline__ uint64_t pkw_smem_desc_k128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFFu);  // start address, 16-byte units
+  d |= (uint64_t)1u << 16;                  // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024u >> 4) << 32;        // stride byte offset: 8 rows x 128 B
+  d |= (uint64_t)1u << 46;                  // descriptor version (Blackwell)
+  d |= (uint64_t)2u << 61;                  // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor, kind::f16: fp32 accumulate, bf16 x bf16, both operands K-major, M x N tile
+__host__ __device__ constexpr uint32_t pkw_instr_desc(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+struct PkwGemmArgs {
+  const float* bias;      // (N,) fp32 or null
+  __nv_bfloat16* out_bf;  // (M, N) bf16 row-major or null
+  float* out_f32;         // (M, N) fp32 row-major or null
+  int M, N, K;            // K % 64 == 0, N % 256 == 0
+  int relu;
+};
+
+// Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
+__global__ void __launch_bounds__(PKW_THREADS, 1)
+pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                    PkwGemmArgs g) {
+  extern __shared__ unsigned char pkw_smem_raw[];
+  // SWIZZLE_128B tiles need 1024-byte alignment
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(pkw_smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* tiles = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + PKW_STAGES * PKW_STAGE_BYTES);
+  uint64_t* empty = full + PKW_STAGES;
+  uint64_t* tfull = empty + PKW_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_mblk = (g.M + PKW_BM - 1) / PKW_BM, n_nblk = g.N / PKW_BN, n_kblk = g.K / PKW_BK;
+  const int n_tiles = n_mblk * n_nblk;
+
+  if (threadIdx.x == 0) {
+    pkw_prefetch_map(&map_a);
+    pkw_prefetch_map(&map_w);
+    for (int i = 0; i < PKW_STAGES; ++i) {
+      pk_mbar_init(full + i, 1);
+      pk_mbar_init(empty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      pk_mbar_init(tfull + i, 1);
+      pk_mbar_init(tempty + i, 4);
+    }
+    pk_fence_mbar_init();
+  }
+  if (warp == 1) pkw_tmem_alloc(tmem_slot, 512);
+  pkw_tc_fence_before();
+  __syncthreads();
+  pkw_tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    int s = 0;
+    uint32_t ph = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int mb = tile / n_nblk, nb = tile - mb * n_nblk;
+      for (int kb = 0; kb < n_kblk; ++kb) {
+        pk_mbar_wait(empty + s, ph ^ 1u);
+        pk_mbar_expect_tx(full + s, PKW_STAGE_BYTES);
+        unsigned char* sa = tiles + s * PKW_STAGE_BYTES;
+        pkw_tma_load_2d(sa, &map_a, kb * PKW_BK, mb * PKW_BM, full + s);
+        pkw_tma_load_2d(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN, full + s);
+        if (++s == PKW_STAGES) {
+          s = 0;
+          ph ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = pkw_instr_desc(PKW_BM, PKW_BN);
+    int s = 0;
+    uint32_t ph = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aph = (uint32_t)(it >> 1) & 1u;
+      pk_mbar_wait(tempty + as, aph ^ 1u);  // the epilogue has drained this accumulator
+      pkw_tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * PKW_BN);
+      for (int kb = 0; kb < n_kblk; ++kb) {
+        pk_mbar_wait(full + s, ph);
+        pkw_tc_fence_after();
+        const uint32_t sa = pk_smem_u32(tiles + s * PKW_STAGE_BYTES);
+        const uint64_t adesc = pkw_smem_desc_k128(sa);
+        const uint64_t bdesc = pkw_smem_desc_k128(sa + PKW_A_BYTES);
+#pragma unroll
+        for (int k = 0; k < PKW_BK / 16; ++k)  // UMMA_K = 16 bf16 = 32 B: +2 in the 16-byte address field
+          pkw_mma(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+        pkw_mma_commit(empty + s);  // frees the stage once these MMAs have read it
+        if (++s == PKW_STAGES) {
+          s = 0;
+          ph ^= 1u;
+        }
+      }
+      pkw_mma_commit(tfull + as);  // accumulator complete
+    }
+  } else if (warp >= 2) {
+    // ===== epilogue: TMEM -> registers -> bias, ReLU -> global =====
+    const int quarter = warp & 3;  // a warp may only touch TMEM lanes 32 * (warp % 4) .. + 31
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int mb = tile / n_nblk, nb = tile - mb * n_nblk;
+      const int as = it & 1;
+      const uint32_t aph = (uint32_t)(it >> 1) & 1u;
+      pk_mbar_wait(tfull + as, aph);
+      pkw_tc_fence_after();
+      const int row = mb * PKW_BM + quarter * 32 + lane;
+      const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * PKW_BN);
+#pragma unroll 1
+      for (int ch = 0; ch < PKW_BN / 32; ++ch) {
+        uint32_t v[32];
+        pkw_tmem_ld32(t0 + (uint32_t)(ch * 32), v);
+        pkw_tmem_ld_wait();
+        const int n0 = nb * PKW_BN + ch * 32;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (g.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + n0 + j));
+            f[j] += bv.x;
+            f[j + 1] += bv.y;
+            f[j + 2] += bv.z;
+            f[j + 3] += bv.w;
+          }
+        }
+        if (g.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        if (row < g.M) {
+          if (g.out_bf != nullptr) {
+            uint4* dst = reinterpret_cast<uint4*>(g.out_bf + (size_t)row * g.N + n0);
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 o;
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(f[j], f[j + 1]);
+              __nv_bfloat162 p1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]);
+              __nv_bfloat162 p3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+              o.x = *reinterpret_cast<uint32_t*>(&p0);
+              o.y = *reinterpret_cast<uint32_t*>(&p1);
+              o.z = *reinterpret_cast<uint32_t*>(&p2);
+              o.w = *reinterpret_cast<uint32_t*>(&p3);
+              dst[j >> 3] = o;
+            }
+          }
+          if (g.out_f32 != nullptr) {
+            float4* dst = reinterpret_cast<float4*>(g.out_f32 + (size_t)row * g.N + n0);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) dst[j >> 2] = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+          }
+        }
+      }
+      pkw_tc_fence_before();
+      __syncwarp();
+      if (lane == 0) pkw_mbar_arrive(tempty + as);
+    }
+  }
+  pkw_tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    pkw_tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ---- packed records -> X (B*A, KPAD) bf16 (feature_extractor.py:40-52 transposed to one row per column) ----
+#define PKW_ENC_WARPS 8
+__host__ __device__ inline unsigned pkw_enc_warp_bytes(int A, int kpad) {
+  return PK_WARP_FIXED_BYTES + 16u + (unsigned)A * (unsigned)kpad * 2u;
+}
+__global__ void __launch_bounds__(PKW_ENC_WARPS * 32)
+pk_wide_encode_kernel(const uint4* __restrict__ packed, int B, int A, int C, int kpad, __nv_bfloat16* __restrict__ X,
+                      int* __restrict__ mask) {
+  extern __shared__ __align__(16) unsigned char enc_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* wa = enc_smem + warp * pkw_enc_warp_bytes(A, kpad);
+  uint4* rec = reinterpret_cast<uint4*>(wa);
+  const uint8_t* r = reinterpret_cast<const uint8_t*>(rec);
+  float* sv = reinterpret_cast<float*>(wa + PK_WARP_REC_BYTES);
+  int* idx = reinterpret_cast<int*>(wa + PK_WARP_REC_BYTES + PK_WARP_SV_BYTES);
+  __nv_bfloat16* rows = reinterpret_cast<__nv_bfloat16*>(wa + PK_WARP_FIXED_BYTES + 16u);  // [A][kpad]
+  const int n16 = A * kpad / 8;  // uint4 chunks of the battle's rows
+  const __nv_bfloat16 one = __float2bfloat16_rn(1.0f);
+  for (long long b = (long long)blockIdx.x * PKW_ENC_WARPS + warp; b < B; b += (long long)gridDim.x * PKW_ENC_WARPS) {
+    __syncwarp();
+    if (lane < 9) rec[lane] = __ldg(packed + b * 9 + lane);
+    uint4* r16 = reinterpret_cast<uint4*>(rows);
+    for (int i = lane; i < n16; i += 32) r16[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    const int n_act = min((int)r[PK_OFF_NACT], A);
+    if (mask != nullptr && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;
+    sv[lane] = pk_state_feature(r, lane);
+    sv[lane + 32] = pk_state_feature(r, lane + 32);
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int e = lane + 32 * it;
+      if (e < 8 * A) {
+        const int c = e >> 3;
+        const int row = c < n_act ? pk_choice_row(r, c, e & 7) : -1;
+        idx[e] = row < 0 ? C : row;
+      }
+    }
+    __syncwarp();
+    for (int k = lane; k < PK_N_STATE; k += 32) {  // state rows fill every column (feature_extractor.py:48)
+      const __nv_bfloat16 v = __float2bfloat16_rn(sv[k]);
+      for (int c = 0; c < A; ++c) rows[c * kpad + k] = v;
+    }
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int e = lane + 32 * it;
+      if (e < 8 * A) {
+        const int row = idx[e];
+        if (row != C) rows[(e >> 3) * kpad + row] = one;
+      }
+    }
+    __syncwarp();
+    uint4* dst = reinterpret_cast<uint4*>(X + (size_t)b * A * kpad);
+    for (int i = lane; i < n16; i += 32) dst[i] = r16[i];
+  }
+}
+
+// ---- head: q[m] = h[m] . w_out + b_out, one warp per row (mlp_model.py:26-28, the 1-channel output conv) ----
+__global__ void __launch_bounds__(256)
+pk_wide_head_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ wout, const float* __restrict__ bout,
+                    int M, int N, float* __restrict__ q) {
+  const int lane = threadIdx.x & 31;
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (m >= M) return;
+  const uint4* row = reinterpret_cast<const uint4*>(h + (size_t)m * N);
+  float s = 0.0f;
+  for (int i = lane; i < N / 8; i += 32) {
+    const uint4 v = __ldg(row + i);
+    const float4 w0 = __ldg(reinterpret_cast<const float4*>(wout + 8 * i));
+    const float4 w1 = __ldg(reinterpret_cast<const float4*>(wout + 8 * i + 4));
+    const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&v);
+    const float2 a = __bfloat1622float2(p[0]), b = __bfloat1622float2(p[1]);
+    const float2 c = __bfloat1622float2(p[2]), d = __bfloat1622float2(p[3]);
+    s = fmaf(a.x, w0.x, s);
+    s = fmaf(a.y, w0.y, s);
+    s = fmaf(b.x, w0.z, s);
+    s = fmaf(b.y, w0.w, s);
+    s = fmaf(c.x, w1.x, s);
+    s = fmaf(c.y, w1.y, s);
+    s = fmaf(d.x, w1.z, s);
+    s = fmaf(d.y, w1.w, s);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) q[m] = s + __ldg(bout);
+}
+
+// fp32 (rows, cols) row-major -> bf16 (rows, cols_pad), zero padded columns
+__global__ void pk_wide_cast_pad_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols,
+                                        int cols_pad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)rows * cols_pad) return;
+  const int r = (int)(i / cols_pad), c = (int)(i - (long long)r * cols_pad);
+  dst[i] = __float2bfloat16_rn(c < cols ? src[(size_t)r * cols + c] : 0.0f);
+}

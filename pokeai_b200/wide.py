@@ -1,0 +1,143 @@
+"""Host side of the wide-network (tensor-core) path: the same MLPModel (mlp_model.py:5-30) at n_channels that
+are a multiple of 256 (BASELINE.json configs[4]: 4 x 2048) runs as bf16 tcgen05 GEMMs with fused bias + ReLU
+(pokeai_b200/csrc/pk_wide.cuh) instead of the fp32 small-net kernel.  No CPU path: everything raises without the
+CUDA library and a device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .ops import SelectSpec, _check_packed, _dev, _stream_ptr, n_channels, packed_to_device
+
+WIDE_MULTIPLE = 256
+
+
+def is_wide(n_channels_: int) -> bool:
+    """True when the network takes the tensor-core path (the fp32 small-net kernel stops at 128 channels)."""
+    return n_channels_ >= WIDE_MULTIPLE and n_channels_ % WIDE_MULTIPLE == 0
+
+
+def gemm_bf16(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+              out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """act(a @ w.T + bias): a (M, K) bf16, w (N, K) bf16 (a state_dict weight cast to bf16), fp32 accumulation."""
+    dev = _dev(a)
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and a.is_contiguous() and w.is_contiguous()
+    M, K = a.shape
+    Nn, K2 = w.shape
+    assert K == K2
+    N.ensure_init(dev.index if dev.index is not None else torch.cuda.current_device())
+    out = torch.empty((M, Nn), dtype=out_dtype, device=dev)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == Nn and bias.is_cuda
+    ob = out.data_ptr() if out_dtype == torch.bfloat16 else None
+    of = out.data_ptr() if out_dtype == torch.float32 else None
+    assert ob is not None or of is not None, "out_dtype must be bfloat16 or float32"
+    N.check(N.lib().pk_gemm_bf16(a.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None, ob, of,
+                                 M, Nn, K, 1 if relu else 0, _stream_ptr(dev)))
+    return out
+
+
+def prepare_wide(state_dict: dict, device) -> tuple:
+    """state_dict (reference key names) -> (prepared uint8 buffer on device, n_layers, n_channels)."""
+    dev = torch.device(device)
+    N.ensure_init(dev.index if dev.index is not None else torch.cuda.current_device())
+    nl = 0
+    while f"layers.{nl}.weight" in state_dict:
+        nl += 1
+    w0 = state_dict["layers.0.weight"]
+    H, Cin = int(w0.shape[0]), int(w0.shape[1])
+    lib = N.lib()
+    nbytes = lib.pk_wide_prepared_bytes(nl, H, Cin)
+    if nbytes == 0:
+        raise ValueError(f"network {nl} x {H} is not supported by the tensor-core path (n_channels % 256 != 0)")
+    keep = []
+    m = N.pk_mlp()
+    m.n_layers, m.n_channels, m.in_channels = nl, H, Cin
+    for i in range(nl):
+        w = state_dict[f"layers.{i}.weight"].detach().to(dev, torch.float32).contiguous()
+        b = state_dict[f"layers.{i}.bias"].detach().to(dev, torch.float32).contiguous()
+        keep += [w, b]
+        m.w[i], m.b[i] = w.data_ptr(), b.data_ptr()
+    wo = state_dict["output.weight"].detach().to(dev, torch.float32).contiguous()
+    bo = state_dict["output.bias"].detach().to(dev, torch.float32).contiguous()
+    keep += [wo, bo]
+    m.w_out, m.b_out = wo.data_ptr(), bo.data_ptr()
+    prepared = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    N.check(lib.pk_wide_prepare(C.byref(m), prepared.data_ptr(), _stream_ptr(dev)))
+    torch.cuda.current_stream(dev).synchronize()  # the fp32 staging copies in `keep` may be freed now
+    return prepared, nl, H
+
+
+def workspace(n_layers: int, H: int, B: int, A: int, device) -> torch.Tensor:
+    nbytes = N.lib().pk_wide_workspace_bytes(n_layers, H, n_channels(), B, A)
+    if nbytes == 0:
+        raise ValueError("unsupported wide-network shape")
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def wide_forward(packed: torch.Tensor, A: int, prepared: torch.Tensor, n_layers: int, H: int,
+                 ws: Optional[torch.Tensor] = None, spec: Optional[SelectSpec] = None,
+                 out_mask: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
+                 out_action: Optional[torch.Tensor] = None):
+    """Packed records (device) -> (mask (B, A) int32, q (B, A) fp32, action (B,) int32)."""
+    dev = _dev(packed)
+    B = _check_packed(packed)
+    if ws is None:
+        ws = workspace(n_layers, H, B, A, dev)
+    mask = out_mask if out_mask is not None else torch.empty((B, A), dtype=torch.int32, device=dev)
+    q = out_q if out_q is not None else torch.empty((B, A), dtype=torch.float32, device=dev)
+    act = out_action if out_action is not None else torch.empty((B,), dtype=torch.int32, device=dev)
+    sp = spec.to_c(B) if spec is not None else None
+    N.check(N.lib().pk_wide_forward(packed.data_ptr(), B, A, prepared.data_ptr(), n_layers, H, ws.data_ptr(),
+                                    mask.data_ptr(), q.data_ptr(), act.data_ptr(),
+                                    C.byref(sp) if sp is not None else None, _stream_ptr(dev)))
+    return mask, q, act
+
+
+class WideRunner:
+    """Batched decisions for a wide MLPModel: host records -> pinned staging -> H2D -> pk_wide_forward -> D2H.
+    The counterpart of the native session the small network uses (Agent.q_and_action_batch dispatches here)."""
+
+    def __init__(self, model, A: int, device):
+        self.device = torch.device(device)
+        self.A = A
+        self.model = model
+        self._prepared = None
+        self._key = None
+        self._cap = 0
+
+    def _ensure(self, n: int) -> None:
+        m = self.model
+        key = tuple((p.data_ptr(), p._version) for p in m.parameters())
+        if self._prepared is None or key != self._key:
+            self._prepared = prepare_wide(m.folded_state_dict(), self.device)[0]
+            self._key = key
+        if n > self._cap:
+            cap = max(n, 2 * self._cap)
+            self._pin = torch.empty((cap, N.PK_OBS_BYTES), dtype=torch.uint8, pin_memory=True)
+            self._dpk = torch.empty((cap, N.PK_OBS_BYTES), dtype=torch.uint8, device=self.device)
+            self._ws = workspace(m.n_layers, m.n_channels, cap, self.A, self.device)
+            self._mask = torch.empty((cap, self.A), dtype=torch.int32, device=self.device)
+            self._q = torch.empty((cap, self.A), dtype=torch.float32, device=self.device)
+            self._act = torch.empty((cap,), dtype=torch.int32, device=self.device)
+            self._hq = torch.empty((cap, self.A), dtype=torch.float32, pin_memory=True)
+            self._ha = torch.empty((cap,), dtype=torch.int32, pin_memory=True)
+            self._cap = cap
+
+    def decide(self, records: np.ndarray, spec: Optional[SelectSpec] = None):
+        n = len(records)
+        self._ensure(n)
+        self._pin.numpy()[:n] = np.ascontiguousarray(records).view(np.uint8).reshape(n, N.PK_OBS_BYTES)
+        self._dpk[:n].copy_(self._pin[:n], non_blocking=True)
+        m = self.model
+        wide_forward(self._dpk[:n], self.A, self._prepared, m.n_layers, m.n_channels, ws=self._ws, spec=spec,
+                     out_mask=self._mask[:n], out_q=self._q[:n], out_action=self._act[:n])
+        self._hq[:n].copy_(self._q[:n], non_blocking=True)
+        self._ha[:n].copy_(self._act[:n], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._hq.numpy()[:n], self._ha.numpy()[:n]

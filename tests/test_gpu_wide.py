@@ -1,0 +1,112 @@
+"""GPU parity tests of the wide-network (tcgen05 tensor-core) path, through the C ABI.
+
+Oracle: the reference's MLPModel arithmetic is torch CPU fp32 (oracle/ref_port.mlp_forward).  The tensor-core
+path rounds operands and activations to bf16 and accumulates in fp32, so two checks are made:
+  * against a bf16-EMULATING fp32 oracle (same roundings, fp32 accumulation on the CPU): tight tolerance, catches
+    any layout / descriptor / pipeline error;
+  * against the plain fp32 oracle: the bf16 tolerance of SURVEY.md 8c (|dq| <= 2e-2), argmax agreement reported.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+def _bf(x: torch.Tensor) -> torch.Tensor:
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+@pytest.mark.parametrize("M,N,K,relu,bias", [(128, 256, 64, False, False), (300, 256, 128, True, True),
+                                             (1000, 512, 640, True, True), (129, 2048, 2048, False, True),
+                                             (4096, 1024, 1024, True, False)])
+def test_gemm_bf16_matches_fp32_matmul_of_bf16_operands(dev, M, N, K, relu, bias):
+    from pokeai_b200 import wide
+    g = torch.Generator().manual_seed(M + N + K)
+    a = _bf(torch.randn((M, K), generator=g))
+    w = _bf(torch.randn((N, K), generator=g) / np.sqrt(K))
+    b = torch.randn((N,), generator=g) if bias else None
+    ref = a @ w.t()
+    if b is not None:
+        ref = ref + b
+    if relu:
+        ref = ref.clamp_min(0)
+    out32 = wide.gemm_bf16(a.to(dev, torch.bfloat16), w.to(dev, torch.bfloat16),
+                           b.to(dev) if b is not None else None, relu=relu, out_dtype=torch.float32)
+    np.testing.assert_allclose(out32.cpu().numpy(), ref.numpy(), rtol=2e-4, atol=2e-4)
+    out16 = wide.gemm_bf16(a.to(dev, torch.bfloat16), w.to(dev, torch.bfloat16),
+                           b.to(dev) if b is not None else None, relu=relu, out_dtype=torch.bfloat16)
+    np.testing.assert_allclose(out16.float().cpu().numpy(), ref.numpy(), rtol=1e-2, atol=1e-2)
+
+
+def test_gemm_refuses_unsupported_shapes(dev):
+    from pokeai_b200 import wide
+    a = torch.zeros((64, 96), dtype=torch.bfloat16, device=dev)
+    w = torch.zeros((256, 96), dtype=torch.bfloat16, device=dev)
+    with pytest.raises(RuntimeError):
+        wide.gemm_bf16(a, w)  # K not a multiple of 64
+    a = torch.zeros((64, 64), dtype=torch.bfloat16, device=dev)
+    w = torch.zeros((100, 64), dtype=torch.bfloat16, device=dev)
+    with pytest.raises(RuntimeError):
+        wide.gemm_bf16(a, w)  # N not a multiple of 256
+
+
+def _emulated_forward(sd, feat, nl):
+    """fp32 CPU forward with the tensor-core path's roundings: bf16 inputs, weights and hidden activations,
+    fp32 accumulation, fp32 biases and head."""
+    B, C, A = feat.shape
+    x = _bf(torch.from_numpy(feat).permute(0, 2, 1).reshape(B * A, C))
+    for i in range(nl):
+        w = _bf(sd[f"layers.{i}.weight"][:, :, 0])
+        x = _bf((x @ w.t() + sd[f"layers.{i}.bias"]).clamp_min(0))
+    q = x @ sd["output.weight"][0, :, 0] + sd["output.bias"][0]
+    return q.reshape(B, A).numpy()
+
+
+@pytest.mark.parametrize("ps,nl,H,B,kind", [(6, 2, 256, 300, "ragged"), (6, 4, 2048, 512, "full"), (3, 3, 512, 77, "ragged")])
+def test_wide_forward_matches_oracle(tables, dev, ps, nl, H, B, kind):
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import ops, wide
+    from pokeai_b200.packed import synth_packed
+    A = 4 + ps - 1
+    rec = synth_packed(B, seed=B + H, party_size=ps, kind=kind, tables=tables)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=H + nl)
+    fo, mo = packed_oracle.encode(rec, ps, tables)
+    with torch.no_grad():
+        q32 = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+        qem = _emulated_forward(sd, fo, nl)
+    prepared, nl2, H2 = wide.prepare_wide(sd, dev)
+    assert (nl2, H2) == (nl, H)
+    m, q, a = wide.wide_forward(ops.packed_to_device(rec, dev), A, prepared, nl, H)
+    torch.cuda.synchronize()
+    qg = q.cpu().numpy()
+    assert np.array_equal(m.cpu().numpy(), mo)                      # masks bit-exact
+    np.testing.assert_allclose(qg, qem, rtol=3e-3, atol=3e-3)       # same roundings: only summation order differs
+    np.testing.assert_allclose(qg, q32, rtol=0, atol=2e-2)          # bf16 tolerance against the fp32 reference
+    assert np.array_equal(a.cpu().numpy(), ref_port.masked_argmax(qg, mo))  # exact argmax of its own Q
+    agree = float((a.cpu().numpy() == ref_port.masked_argmax(q32, mo)).mean())
+    assert agree > 0.9, f"argmax agreement with the fp32 reference only {agree:.3f}"
+
+
+def test_wide_runner_host_records(tables, dev):
+    """the host-buffer API (records in, numpy out) used by Agent.act_batch for wide models"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import wide
+    from pokeai_b200.mlp_model import MLPModel
+    from pokeai_b200.packed import synth_packed
+    torch.manual_seed(1)
+    model = MLPModel((tables.n_channels, 9), 9, n_layers=2, n_channels=256).eval()
+    rec = synth_packed(100, seed=5, party_size=6, kind="ragged", tables=tables)
+    r = wide.WideRunner(model, 9, dev)
+    q, a = r.decide(rec)
+    fo, mo = packed_oracle.encode(rec, 6, tables)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        q32 = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    np.testing.assert_allclose(q, q32, rtol=0, atol=2e-2)
+    assert np.array_equal(a, ref_port.masked_argmax(q, mo))
