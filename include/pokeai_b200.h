@@ -255,6 +255,20 @@ PK_API int pk_wide_forward(const pk_obs* packed, int B, int A, const void* wide_
                            void* workspace, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
                            void* stream);
 
+/* Y (M,N) fp32 = A^T . W with A (K,M) and W (K,N) bf16 row-major: the contraction index is the ROW of both operands
+ * (weight gradient dW = dZ^T H).  M % 8 == 0, N % 32 == 0; any K (zero-filled tail). */
+PK_API int pk_gemm_bf16_tn(const void* a_km_bf16, const void* w_kn_bf16, float* out_f32, int M, int N, int K, void* stream);
+/* Forward + backward of the wide network: loss.backward() of Trainer._update (trainer.py:192) for MLPModel at 4 x 2048.
+ * pk_wide_train_forward keeps every layer's bf16 activations in the workspace and returns q (B,A); the caller
+ * forms dq = d loss / d q (B*A fp32, zero for columns that carry no loss -- trainer.py:163 gathers the chosen one);
+ * pk_wide_train_backward returns the flat fp32 gradient in state_dict order (pk_mlp_param_floats floats).
+ * B*A must be a multiple of 8.  Gradients are bit-reproducible (no atomics). */
+PK_API size_t pk_wide_train_workspace_bytes(int n_layers, int n_channels, int in_channels, int B, int A);
+PK_API int pk_wide_train_forward(const pk_obs* packed, int B, int A, const void* wide_prepared, int n_layers,
+                                 int n_channels, void* workspace, int32_t* mask, float* q, void* stream);
+PK_API int pk_wide_train_backward(const void* wide_prepared, int n_layers, int n_channels, int B, int A, void* workspace,
+                                  const float* dq, float* grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

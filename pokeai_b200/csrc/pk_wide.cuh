@@ -97,20 +97,37 @@ __device__ __forceinline__ uint64_t pkw_smem_desc_k128(uint32_t saddr) {
   d |= (uint64_t)2u << 61;                  // SWIZZLE_128B
   return d;
 }
-// instruction descriptor, kind::f16: fp32 accumulate, bf16 x bf16, both operands K-major, M x N tile
-__host__ __device__ constexpr uint32_t pkw_instr_desc(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// MN-major operand (the contraction index is the ROW of the row-major source, e.g. dW = dZ^T H): the tile is a
+// row of 64-element-wide TMA boxes, each box 64 k-rows x 128 B; 8-row groups 1024 B apart (stride byte offset),
+// successive 64-element chunks of the M/N extent one box = 8192 B apart (leading byte offset)
+__device__ __forceinline__ uint64_t pkw_smem_desc_mn128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFFu);
+  d |= (uint64_t)(8192u >> 4) << 16;
+  d |= (uint64_t)(1024u >> 4) << 32;
+  d |= (uint64_t)1u << 46;
+  d |= (uint64_t)2u << 61;
+  return d;
+}
+// instruction descriptor, kind::f16: fp32 accumulate, bf16 x bf16, M x N tile; mn_major != 0: both operands MN-major
+__host__ __device__ constexpr uint32_t pkw_instr_desc(int M, int N, int mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (mn_major ? (3u << 15) : 0u) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
 }
 
 struct PkwGemmArgs {
   const float* bias;      // (N,) fp32 or null
   __nv_bfloat16* out_bf;  // (M, N) bf16 row-major or null
   float* out_f32;         // (M, N) fp32 row-major or null
-  int M, N, K;            // K % 64 == 0, N % 256 == 0
+  const __nv_bfloat16* relu_mask;  // (M, N) bf16 or null: out = mask > 0 ? acc : 0 (backward through a ReLU)
+  int M, N, K;            // N % 32 == 0; tails in M, N (to 256) and K (to 64) are zero-filled by TMA
   int relu;
 };
 
-// Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
+// MN == 0:  Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
+// MN == 1:  Y (M, N) = A (K, M)^T . W (K, N): both operands bf16 row-major with the CONTRACTION index as the row
+//           (weight gradient dW = dZ^T H); the tensor maps then have 64 x 64 boxes.
+template <int MN>
 __global__ void __launch_bounds__(PKW_THREADS, 1)
 pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     PkwGemmArgs g) {
@@ -125,7 +142,8 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_mblk = (g.M + PKW_BM - 1) / PKW_BM, n_nblk = g.N / PKW_BN, n_kblk = g.K / PKW_BK;
+  const int n_mblk = (g.M + PKW_BM - 1) / PKW_BM, n_nblk = (g.N + PKW_BN - 1) / PKW_BN,
+            n_kblk = (g.K + PKW_BK - 1) / PKW_BK;
   const int n_tiles = n_mblk * n_nblk;
 
   if (threadIdx.x == 0) {
@@ -157,8 +175,17 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         pk_mbar_wait(empty + s, ph ^ 1u);
         pk_mbar_expect_tx(full + s, PKW_STAGE_BYTES);
         unsigned char* sa = tiles + s * PKW_STAGE_BYTES;
-        pkw_tma_load_2d(sa, &map_a, kb * PKW_BK, mb * PKW_BM, full + s);
-        pkw_tma_load_2d(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN, full + s);
+        if constexpr (MN == 0) {
+          pkw_tma_load_2d(sa, &map_a, kb * PKW_BK, mb * PKW_BM, full + s);
+          pkw_tma_load_2d(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN, full + s);
+        } else {
+#pragma unroll
+          for (int j = 0; j < PKW_BM / 64; ++j)
+            pkw_tma_load_2d(sa + j * 8192, &map_a, mb * PKW_BM + 64 * j, kb * PKW_BK, full + s);
+#pragma unroll
+          for (int j = 0; j < PKW_BN / 64; ++j)
+            pkw_tma_load_2d(sa + PKW_A_BYTES + j * 8192, &map_w, nb * PKW_BN + 64 * j, kb * PKW_BK, full + s);
+        }
         if (++s == PKW_STAGES) {
           s = 0;
           ph ^= 1u;
@@ -167,7 +194,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     }
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer =====
-    constexpr uint32_t idesc = pkw_instr_desc(PKW_BM, PKW_BN);
+    constexpr uint32_t idesc = pkw_instr_desc(PKW_BM, PKW_BN, MN);
     int s = 0;
     uint32_t ph = 0;
     int it = 0;
@@ -181,11 +208,14 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         pk_mbar_wait(full + s, ph);
         pkw_tc_fence_after();
         const uint32_t sa = pk_smem_u32(tiles + s * PKW_STAGE_BYTES);
-        const uint64_t adesc = pkw_smem_desc_k128(sa);
-        const uint64_t bdesc = pkw_smem_desc_k128(sa + PKW_A_BYTES);
+        const uint64_t adesc = MN ? pkw_smem_desc_mn128(sa) : pkw_smem_desc_k128(sa);
+        const uint64_t bdesc = MN ? pkw_smem_desc_mn128(sa + PKW_A_BYTES) : pkw_smem_desc_k128(sa + PKW_A_BYTES);
+        // UMMA_K = 16: K-major advances 16 bf16 = 32 B inside the swizzle atom (+2 in the 16-byte address field),
+        // MN-major advances 16 k-rows of 128 B = 2048 B (+128)
+        constexpr uint64_t kstep = MN ? 128u : 2u;
 #pragma unroll
-        for (int k = 0; k < PKW_BK / 16; ++k)  // UMMA_K = 16 bf16 = 32 B: +2 in the 16-byte address field
-          pkw_mma(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+        for (int k = 0; k < PKW_BK / 16; ++k)
+          pkw_mma(d_tmem, adesc + kstep * (uint64_t)k, bdesc + kstep * (uint64_t)k, idesc, (kb | k) != 0 ? 1u : 0u);
         pkw_mma_commit(empty + s);  // frees the stage once these MMAs have read it
         if (++s == PKW_STAGES) {
           s = 0;
@@ -212,6 +242,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         pkw_tmem_ld32(t0 + (uint32_t)(ch * 32), v);
         pkw_tmem_ld_wait();
         const int n0 = nb * PKW_BN + ch * 32;
+        if (n0 >= g.N) break;  // N tail (warp-uniform)
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
@@ -228,6 +259,20 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         if (g.relu) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        if (g.relu_mask != nullptr && row < g.M) {
+          const uint4* mp = reinterpret_cast<const uint4*>(g.relu_mask + (size_t)row * g.N + n0);
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const uint4 mv = __ldg(mp + (j >> 3));
+            const __nv_bfloat162* mh = reinterpret_cast<const __nv_bfloat162*>(&mv);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float2 mf = __bfloat1622float2(mh[t]);
+              if (!(mf.x > 0.0f)) f[j + 2 * t] = 0.0f;
+              if (!(mf.y > 0.0f)) f[j + 2 * t + 1] = 0.0f;
+            }
+          }
         }
         if (row < g.M) {
           if (g.out_bf != nullptr) {
@@ -359,4 +404,96 @@ __global__ void pk_wide_cast_pad_kernel(const float* __restrict__ src, __nv_bflo
   if (i >= (long long)rows * cols_pad) return;
   const int r = (int)(i / cols_pad), c = (int)(i - (long long)r * cols_pad);
   dst[i] = __float2bfloat16_rn(c < cols ? src[(size_t)r * cols + c] : 0.0f);
+}
+
+// ---- backward helpers (Trainer._update's loss.backward(), trainer.py:192, for the wide network) -------------
+// fp32 (rows, cols) -> bf16 (cols, rows): the transposed weight copy read by the dH GEMM
+__global__ void pk_wide_transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows,
+                                              int cols) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < rows && c < cols) ? src[(size_t)r * cols + c] : 0.0f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (c < cols && r < rows) dst[(size_t)c * rows + r] = __float2bfloat16_rn(tile[threadIdx.x][i]);
+  }
+}
+
+// dZ_L[m][n] = dq[m] * w_out[n] * (h[m][n] > 0)   (backward of the 1-channel head through the last ReLU)
+__global__ void __launch_bounds__(256)
+pk_wide_dz_head_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ dq, const float* __restrict__ wout,
+                       int M, int N, __nv_bfloat16* __restrict__ dz) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one thread per 8 elements
+  const long long total = (long long)M * N / 8;
+  if (i >= total) return;
+  const long long e = i * 8;
+  const int m = (int)(e / N), n = (int)(e - (long long)m * N);
+  const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + e));
+  const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv);
+  const float d = __ldg(dq + m);
+  const float4 w0 = __ldg(reinterpret_cast<const float4*>(wout + n));
+  const float4 w1 = __ldg(reinterpret_cast<const float4*>(wout + n + 4));
+  const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+  uint4 o;
+  __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const float2 hf = __bfloat1622float2(hp[t]);
+    op[t] = __floats2bfloat162_rn(hf.x > 0.0f ? d * w[2 * t] : 0.0f, hf.y > 0.0f ? d * w[2 * t + 1] : 0.0f);
+  }
+  *reinterpret_cast<uint4*>(dz + e) = o;
+}
+
+// partial[s][n] = sum over the rows of split s of scale[m] * z[m][n]  (scale == null: 1).  Fixed order: each
+// thread owns two columns and walks its rows in order; the splits are summed in order by the finish kernel.
+#define PKW_COLSUM_SPLITS 64
+__global__ void __launch_bounds__(128)
+pk_wide_colsum_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ scale, int M, int N,
+                      float* __restrict__ partial) {
+  const int n = (blockIdx.x * 128 + threadIdx.x) * 2;
+  if (n >= N) return;
+  const int s = blockIdx.y;
+  const int rows_per = (M + PKW_COLSUM_SPLITS - 1) / PKW_COLSUM_SPLITS;
+  const int m0 = s * rows_per, m1 = min(M, m0 + rows_per);
+  float a0 = 0.0f, a1 = 0.0f;
+  for (int m = m0; m < m1; ++m) {
+    const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(z + (size_t)m * N + n));
+    const float sc = scale != nullptr ? __ldg(scale + m) : 1.0f;
+    a0 = fmaf(sc, v.x, a0);
+    a1 = fmaf(sc, v.y, a1);
+  }
+  partial[(size_t)s * N + n] = a0;
+  partial[(size_t)s * N + n + 1] = a1;
+}
+__global__ void pk_wide_colsum_finish_kernel(const float* __restrict__ partial, int N, float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float a = 0.0f;
+  for (int s = 0; s < PKW_COLSUM_SPLITS; ++s) a += partial[(size_t)s * N + n];
+  out[n] = a;
+}
+// out[0] = sum_m dq[m] (gradient of output.bias), one block, fixed order
+__global__ void __launch_bounds__(256) pk_wide_sum_kernel(const float* __restrict__ x, int M, float* __restrict__ out) {
+  __shared__ float sh[256];
+  float a = 0.0f;
+  for (int m = threadIdx.x; m < M; m += 256) a += x[m];
+  sh[threadIdx.x] = a;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = sh[0];
+}
+// (rows, cols_pad) fp32 -> (rows, cols) fp32: drops the K padding of layer 0's weight gradient
+__global__ void pk_wide_compact_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int cols,
+                                       int cols_pad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)rows * cols) return;
+  const int r = (int)(i / cols), c = (int)(i - (long long)r * cols);
+  dst[i] = src[(size_t)r * cols_pad + c];
 }

@@ -141,3 +141,47 @@ class WideRunner:
         self._ha[:n].copy_(self._act[:n], non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return self._hq.numpy()[:n], self._ha.numpy()[:n]
+
+
+# ---- forward + backward (Trainer._update's loss.backward() for the wide network) ---------------------------------
+def gemm_bf16_tn(a_km: torch.Tensor, w_kn: torch.Tensor) -> torch.Tensor:
+    """a_km.T @ w_kn in fp32: a_km (K, M) bf16, w_kn (K, N) bf16 -- the weight-gradient contraction dW = dZ^T H."""
+    dev = _dev(a_km)
+    assert a_km.dtype == torch.bfloat16 and w_kn.dtype == torch.bfloat16 and a_km.is_contiguous() and w_kn.is_contiguous()
+    K, M = a_km.shape
+    K2, Nn = w_kn.shape
+    assert K == K2
+    out = torch.empty((M, Nn), dtype=torch.float32, device=dev)
+    N.check(N.lib().pk_gemm_bf16_tn(a_km.data_ptr(), w_kn.data_ptr(), out.data_ptr(), M, Nn, K, _stream_ptr(dev)))
+    return out
+
+
+def train_workspace(n_layers: int, H: int, B: int, A: int, device) -> torch.Tensor:
+    nbytes = N.lib().pk_wide_train_workspace_bytes(n_layers, H, n_channels(), B, A)
+    if nbytes == 0:
+        raise ValueError("unsupported wide-network shape")
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def train_forward(packed: torch.Tensor, A: int, prepared: torch.Tensor, n_layers: int, H: int, ws: torch.Tensor,
+                  out_q: Optional[torch.Tensor] = None, out_mask: Optional[torch.Tensor] = None):
+    """Forward that keeps the activations in `ws` for train_backward.  Returns (mask (B, A), q (B, A))."""
+    dev = _dev(packed)
+    B = _check_packed(packed)
+    mask = out_mask if out_mask is not None else torch.empty((B, A), dtype=torch.int32, device=dev)
+    q = out_q if out_q is not None else torch.empty((B, A), dtype=torch.float32, device=dev)
+    N.check(N.lib().pk_wide_train_forward(packed.data_ptr(), B, A, prepared.data_ptr(), n_layers, H, ws.data_ptr(),
+                                          mask.data_ptr(), q.data_ptr(), _stream_ptr(dev)))
+    return mask, q
+
+
+def train_backward(prepared: torch.Tensor, n_layers: int, H: int, B: int, A: int, ws: torch.Tensor, dq: torch.Tensor,
+                   out_grad: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dq (B, A) fp32 = d loss / d q -> flat fp32 gradient in state_dict order."""
+    dev = _dev(dq)
+    assert dq.dtype == torch.float32 and dq.is_contiguous() and dq.numel() == B * A
+    n = N.lib().pk_mlp_param_floats(n_layers, H, n_channels())
+    grad = out_grad if out_grad is not None else torch.empty(n, dtype=torch.float32, device=dev)
+    N.check(N.lib().pk_wide_train_backward(prepared.data_ptr(), n_layers, H, B, A, ws.data_ptr(), dq.data_ptr(),
+                                           grad.data_ptr(), _stream_ptr(dev)))
+    return grad

@@ -24,7 +24,8 @@ def _bf(x: torch.Tensor) -> torch.Tensor:
 
 @pytest.mark.parametrize("M,N,K,relu,bias", [(128, 256, 64, False, False), (300, 256, 128, True, True),
                                              (1000, 512, 640, True, True), (129, 2048, 2048, False, True),
-                                             (4096, 1024, 1024, True, False)])
+                                             (4096, 1024, 1024, True, False), (64, 256, 96, False, True),
+                                             (300, 96, 200, True, True), (777, 640, 2048, False, False)])
 def test_gemm_bf16_matches_fp32_matmul_of_bf16_operands(dev, M, N, K, relu, bias):
     from pokeai_b200 import wide
     g = torch.Generator().manual_seed(M + N + K)
@@ -46,14 +47,14 @@ def test_gemm_bf16_matches_fp32_matmul_of_bf16_operands(dev, M, N, K, relu, bias
 
 def test_gemm_refuses_unsupported_shapes(dev):
     from pokeai_b200 import wide
-    a = torch.zeros((64, 96), dtype=torch.bfloat16, device=dev)
-    w = torch.zeros((256, 96), dtype=torch.bfloat16, device=dev)
+    a = torch.zeros((64, 100), dtype=torch.bfloat16, device=dev)
+    w = torch.zeros((256, 100), dtype=torch.bfloat16, device=dev)
     with pytest.raises(RuntimeError):
-        wide.gemm_bf16(a, w)  # K not a multiple of 64
+        wide.gemm_bf16(a, w)  # K not a multiple of 8 (TMA row pitch)
     a = torch.zeros((64, 64), dtype=torch.bfloat16, device=dev)
     w = torch.zeros((100, 64), dtype=torch.bfloat16, device=dev)
     with pytest.raises(RuntimeError):
-        wide.gemm_bf16(a, w)  # N not a multiple of 256
+        wide.gemm_bf16(a, w)  # N not a multiple of 32
 
 
 def _emulated_forward(sd, feat, nl):
@@ -110,3 +111,83 @@ def test_wide_runner_host_records(tables, dev):
         q32 = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
     np.testing.assert_allclose(q, q32, rtol=0, atol=2e-2)
     assert np.array_equal(a, ref_port.masked_argmax(q, mo))
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 640, 1000), (2048, 2048, 4104), (136, 32, 72)])
+def test_gemm_tn_matches_fp32_matmul_of_bf16_operands(dev, M, N, K):
+    """the contraction-over-rows GEMM (both operands MN-major in shared memory) used for weight gradients"""
+    from pokeai_b200 import wide
+    g = torch.Generator().manual_seed(M + N + K)
+    a = _bf(torch.randn((K, M), generator=g))
+    w = _bf(torch.randn((K, N), generator=g) / np.sqrt(K))
+    ref = a.t() @ w
+    out = wide.gemm_bf16_tn(a.to(dev, torch.bfloat16), w.to(dev, torch.bfloat16))
+    np.testing.assert_allclose(out.cpu().numpy(), ref.numpy(), rtol=3e-4, atol=3e-4)
+
+
+def _emulated_backward(sd, feat, nl, dq):
+    """Gradients with the tensor-core path's roundings (bf16 activations, weights and dZ; fp32 accumulation),
+    by hand: the same chain rule as autograd through mlp_forward."""
+    B, C, A = feat.shape
+    hs = [_bf(torch.from_numpy(feat).permute(0, 2, 1).reshape(B * A, C))]
+    for i in range(nl):
+        w = _bf(sd[f"layers.{i}.weight"][:, :, 0])
+        hs.append(_bf((hs[-1] @ w.t() + sd[f"layers.{i}.bias"]).clamp_min(0)))
+    d = torch.from_numpy(dq).reshape(-1)
+    wout = sd["output.weight"][0, :, 0]
+    g = {"output.weight": (d[:, None] * hs[-1]).sum(0)[None, :, None], "output.bias": d.sum()[None]}
+    dz = _bf(d[:, None] * wout[None, :] * (hs[-1] > 0))
+    for i in range(nl - 1, -1, -1):
+        g[f"layers.{i}.weight"] = (dz.t() @ hs[i])[:, :, None]
+        g[f"layers.{i}.bias"] = dz.sum(0)
+        if i > 0:
+            dz = _bf((dz @ _bf(sd[f"layers.{i}.weight"][:, :, 0])) * (hs[i] > 0))
+    return g
+
+
+@pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 256, 64), (6, 4, 512, 200), (4, 3, 256, 8)])
+def test_wide_backward_matches_oracle(tables, dev, ps, nl, H, B):
+    """flat gradient of sum(dq * q) against (a) the hand-derived bf16-emulating oracle (tight) and (b) torch CPU fp32
+    autograd through the reference forward (bf16 tolerance, relative to each tensor's norm)"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import ops, wide
+    from pokeai_b200.packed import synth_packed
+    A = 4 + ps - 1
+    rec = synth_packed(B, seed=3 * B + H, party_size=ps, kind="ragged", tables=tables)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=H + nl)
+    fo, mo = packed_oracle.encode(rec, ps, tables)
+    rng = np.random.default_rng(B)
+    dq = (rng.standard_normal((B, A)) * (rng.random((B, A)) < 0.3)).astype(np.float32)  # sparse, like the chosen column
+    # (b) fp32 autograd
+    params = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    (ref_port.mlp_forward(params, torch.from_numpy(fo)) * torch.from_numpy(dq)).sum().backward()
+    # (a) emulated
+    gem = _emulated_backward(sd, fo, nl, dq)
+    prepared, _, _ = wide.prepare_wide(sd, dev)
+    ws = wide.train_workspace(nl, H, B, A, dev)
+    m, q = wide.train_forward(ops.packed_to_device(rec, dev), A, prepared, nl, H, ws)
+    grad = wide.train_backward(prepared, nl, H, B, A, ws, torch.from_numpy(dq).to(dev))
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        q32 = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    np.testing.assert_allclose(q.cpu().numpy(), q32, rtol=0, atol=2e-2)
+    flat = grad.cpu()
+    off = 0
+    for k, v in sd.items():  # state_dict order
+        n = v.numel()
+        gk = flat[off:off + n].reshape(v.shape)
+        off += n
+        scale = float(gem[k].abs().max()) + 1e-12
+        err_em = float((gk - gem[k]).abs().max()) / scale
+        assert err_em < 5e-3, f"{k}: {err_em:.2e} of the tensor's max against the bf16-emulating oracle"
+        ref = params[k].grad
+        # bf16 tolerance against fp32 autograd: operands, activations and dZ are rounded to bf16 (2^-9 relative each) and
+        # ReLU gates of near-zero pre-activations can flip, so the bound is on the tensor as a whole
+        rel = float((gk - ref).norm() / (ref.norm() + 1e-12))
+        cos = float((gk * ref).sum() / (gk.norm() * ref.norm() + 1e-20))
+        print(f"{k}: emulated-oracle err {err_em:.2e}, fp32 rel {rel:.3f}, cos {cos:.5f}")
+        assert rel < 0.15 and cos > 0.99, f"{k}: relative error {rel:.3f}, cosine {cos:.4f} against fp32 autograd"
+    assert off == flat.numel()
+    # bit-reproducible: a second backward gives the same bits
+    grad2 = wide.train_backward(prepared, nl, H, B, A, ws, torch.from_numpy(dq).to(dev))
+    assert torch.equal(grad, grad2)
