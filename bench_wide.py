@@ -45,7 +45,13 @@ def parse_args():
     p.add_argument("--layers", type=int, default=4)
     p.add_argument("--channels", type=int, default=2048)
     p.add_argument("--cpu-seconds", type=float, default=10.0)
+    p.add_argument("--mode", default="forward", choices=["forward", "train"],
+                   help="forward: decisions (encode + forward + argmax); train: forward + backward to the flat gradient")
     return p.parse_args()
+
+
+def N_params(nl, H, Cn):
+    return H * Cn + H + (nl - 1) * (H * H + H) + H + 1
 
 
 def tensor_peak():
@@ -130,8 +136,20 @@ def main():
     q = torch.empty((B, A), dtype=torch.float32, device=dev)
     act = torch.empty((B,), dtype=torch.int32, device=dev)
 
+    train = args.mode == "train"
+    if train:
+        del ws
+        ws = wide.train_workspace(nl, H, B, A, dev)
+        g = torch.Generator().manual_seed(1)
+        dq = (torch.randn((B, A), generator=g) / (B * A)).to(dev)  # d loss / d q of a mean-reduced loss, resident
+        grad = torch.empty(N_params(nl, H, Cn), dtype=torch.float32, device=dev)
+
     def step(i):
-        wide.wide_forward(pk[i % n_rot], A, prepared, nl, H, ws=ws, out_mask=mask, out_q=q, out_action=act)
+        if train:
+            wide.train_forward(pk[i % n_rot], A, prepared, nl, H, ws, out_q=q, out_mask=mask)
+            wide.train_backward(prepared, nl, H, B, A, ws, dq, out_grad=grad)
+        else:
+            wide.wide_forward(pk[i % n_rot], A, prepared, nl, H, ws=ws, out_mask=mask, out_q=q, out_action=act)
 
     sampler = B0.ClockSampler(local_rank)
     sampler.start()
@@ -150,33 +168,54 @@ def main():
     barrier()
     dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
     clocks = sampler.summary(t0, t1)
-    checksum = int(act.sum().item())
+    checksum = float(grad.abs().sum().item()) if train else int(act.sum().item())
 
-    runner = wide.WideRunner(model, A, dev)
+    if train:
+        pin = torch.empty((B, 144), dtype=torch.uint8, pin_memory=True)
+        dpk = torch.empty((B, 144), dtype=torch.uint8, device=dev)
+        hq = torch.empty((B, A), dtype=torch.float32, pin_memory=True)
+
+        def e2e_step(i):
+            pin.numpy()[:] = np.ascontiguousarray(recs[i % n_rot]).view(np.uint8).reshape(B, 144)
+            dpk.copy_(pin, non_blocking=True)
+            wide.train_forward(dpk, A, prepared, nl, H, ws, out_q=q, out_mask=mask)
+            wide.train_backward(prepared, nl, H, B, A, ws, dq, out_grad=grad)
+            hq.copy_(q, non_blocking=True)  # the Q values the loss is formed from
+            torch.cuda.current_stream(dev).synchronize()
+        api = "host records -> pinned staging, H2D, pk_wide_train_forward, pk_wide_train_backward, D2H of Q, sync"
+    else:
+        runner = wide.WideRunner(model, A, dev)
+
+        def e2e_step(i):
+            runner.decide(recs[i % n_rot])
+        api = "WideRunner.decide(host records): pinned staging, H2D, pk_wide_forward, D2H of Q and actions, sync"
     for i in range(3):
-        runner.decide(recs[i % n_rot])
+        e2e_step(i)
     torch.cuda.synchronize()
     barrier()
     te0 = time.perf_counter()
     for i in range(args.steps):
-        runner.decide(recs[i % n_rot])
+        e2e_step(i)
     te = max_over_ranks(time.perf_counter() - te0)
     barrier()
     sampler.stop()
     e2e = {"value": B * world * args.steps / te, "unit": UNIT, "h2d_bytes_per_step": B * 144,
-           "d2h_bytes_per_step": B * A * 4 + B * 4, "ms_per_step": te / args.steps * 1e3,
-           "api": "WideRunner.decide(host records): pinned staging, H2D, pk_wide_forward, D2H of Q and actions, sync"}
+           "d2h_bytes_per_step": B * A * 4 + (0 if train else B * 4), "ms_per_step": te / args.steps * 1e3, "api": api}
     cpu = None
-    if rank == 0 and world == 1 and args.cpu_seconds > 0:
+    if rank == 0 and world == 1 and args.cpu_seconds > 0 and not train:
         cpu = cpu_baseline(nl, H, args.cpu_seconds)
     if rank == 0:
         ms = dev_ms / args.steps
         M = B * A
         flops = 2.0 * M * H * (Cn + (nl - 1) * H + 1)  # useful FLOPs: true K = 617 in layer 0, + the head
+        if train:  # + dW of every layer (same FLOPs as its forward) + dX of every layer but the first + head
+            flops += 2.0 * M * H * (Cn + (nl - 1) * H + 1) + 2.0 * M * H * (nl - 1) * H
         peak, src = tensor_peak()
         ach = flops / (ms * 1e-3) / 1e12
         line = {
-            "metric": METRIC, "value": B * world * args.steps / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "metric": METRIC if not train else
+            "samples/sec, wide net 4x2048 forward + backward (encode + tensor-core MLP + flat gradient)",
+            "value": B * world * args.steps / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16 (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": f"wide policy net {nl}x{H}, {B} synthetic battle states per GPU = {M} GEMM rows "
@@ -186,7 +225,7 @@ def main():
                        "l2": f"activations are {M * H * 2 / 1e6:.0f} MB per layer (> the 126 MB L2); {n_rot} rotating inputs"},
             "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                          "traffic": None, "kernel": "pk_wide_gemm_kernel", "flops_per_step": flops, "peak_source": src},
-            "e2e": e2e, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": args.steps * (nl + 3),
+            "e2e": e2e, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": args.steps * ((nl + 2) + (5 * nl + 4) if train else (nl + 3)), "mode": args.mode,
             "checksum": checksum,
         }
         print(json.dumps(line), flush=True)

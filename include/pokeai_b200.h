@@ -146,6 +146,11 @@ PK_API int pk_debug_set_trace(unsigned long long* device_buffer);
  * materialised (the measured optimum, profiles/r01_pair_vs_single.txt).  Results are identical up to fp32
  * summation order. */
 PK_API int pk_debug_set_pairing(int mode);
+/* Tuning / test aid: 1 runs the 64-channel hidden layers of pk_decide's one-battle-per-warp kernel on the warp-level
+ * tensor path (mma.sync tf32 with a 3-term hi/lo split: fp32-accurate, Q stays within the 1e-5 tolerance); 0 (default)
+ * keeps them on the FP32 pipe (FFMA2).  Measured on B200 (profiles/r01_hidden_tc.txt): the legacy mma.sync path is no
+ * faster than FFMA2 here (4.2 vs 4.7 us per 16 battles, lost again in the longer prologue), so it is off by default. */
+PK_API int pk_debug_set_hidden_tc(int on);
 /* Number of SMs of the initialised device (grid sizing information for callers). */
 PK_API int pk_sm_count(void);
 

@@ -56,6 +56,7 @@ _SIGNATURES = {
     "pk_init": (C.c_int, [C.POINTER(pk_tables), _i]),
     "pk_debug_set_trace": (C.c_int, [_vp]),
     "pk_debug_set_pairing": (C.c_int, [_i]),
+    "pk_debug_set_hidden_tc": (C.c_int, [_i]),
     "pk_n_channels": (C.c_int, []),
     "pk_sm_count": (C.c_int, []),
     "pk_mlp_prepared_floats": (_sz, [_i, _i, _i]),

@@ -224,6 +224,89 @@ __device__ __forceinline__ void pk_fma_vec(float (&acc)[CPL], const float (&w)[C
   }
 }
 
+// ---- hidden layer on the warp-level tensor path (64 channels): 3xTF32 split, fp32 accuracy --------------------
+// D (64 channels x <= 16 columns) = W (64 x 64) . h (64 x columns) with mma.sync.m16n8k8 tf32.  Every fp32 operand is
+// split x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and the product is hi*hi + lo*hi + hi*lo with fp32
+// accumulation: the dropped lo*lo term is 2^-22 relative, so Q stays inside the 1e-5 fp32 tolerance while the
+// 36 864 FMAs per battle leave the FP32 pipe (profiles/r01_trace_phases.txt: that pipe bounded the kernel).
+// The weight fragments are laid out once per CTA in the order the lanes consume them: wfrag[kstep][mtile][hi/lo][lane].
+#define PK_TC_HS 68                // hbuf row stride in floats: 4 * col + k makes the B-fragment loads conflict-free
+#define PK_TC_WFRAG_BYTES 32768u   // 8 k-steps x 4 m-tiles x {hi, lo} x 32 lanes x 16 B
+__device__ __forceinline__ uint32_t pk_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void pk_mma_tf32(float (&d)[4], const uint4& a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+               "{%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b0), "r"(b1));
+}
+// prologue: W^T [k][64] (prepared layout) -> fragment order, split into hi / lo
+__device__ __forceinline__ void pk_tc_build_wfrag(const float* __restrict__ wt, uint4* wfrag) {
+  for (int e = threadIdx.x; e < 8 * 4 * 32; e += blockDim.x) {
+    const int ln = e & 31, mt = (e >> 5) & 3, s = e >> 7;
+    const int j = 16 * mt + (ln >> 2), k = 8 * s + (ln & 3);
+    const float w[4] = {__ldg(wt + k * 64 + j), __ldg(wt + k * 64 + j + 8), __ldg(wt + (k + 4) * 64 + j),
+                        __ldg(wt + (k + 4) * 64 + j + 8)};
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      hi[i] = pk_tf32(w[i]);
+      lo[i] = pk_tf32(w[i] - __uint_as_float(hi[i]));
+    }
+    wfrag[((s * 4 + mt) * 2 + 0) * 32 + ln] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    wfrag[((s * 4 + mt) * 2 + 1) * 32 + ln] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+}
+// d[mt][nt][0..3]: channel 16*mt + lane/4 (+8 for [2],[3]), column 8*nt + 2*(lane%4) (+1 for [1],[3]); pre-activation
+template <int A>
+__device__ __forceinline__ void pk_hidden_tc(const uint4* wfrag, const float* bias, const float* hb,
+                                             float (&d)[4][(A + 7) / 8][4], int lane) {
+  constexpr int NT = (A + 7) / 8;
+  const int g4 = lane >> 2, t4 = lane & 3;
+#pragma unroll
+  for (int mt = 0; mt < 4; ++mt) {
+    const float b0 = bias[16 * mt + g4], b1 = bias[16 * mt + g4 + 8];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      d[mt][nt][0] = b0;
+      d[mt][nt][1] = b0;
+      d[mt][nt][2] = b1;
+      d[mt][nt][3] = b1;
+    }
+  }
+#pragma unroll 2
+  for (int s = 0; s < 8; ++s) {
+    uint32_t bh[NT][2], bl[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int col = 8 * nt + g4;
+      float x0 = 0.0f, x1 = 0.0f;
+      if (col < A) {
+        x0 = hb[col * PK_TC_HS + 8 * s + t4];
+        x1 = hb[col * PK_TC_HS + 8 * s + t4 + 4];
+      }
+      bh[nt][0] = pk_tf32(x0);
+      bh[nt][1] = pk_tf32(x1);
+      bl[nt][0] = pk_tf32(x0 - __uint_as_float(bh[nt][0]));
+      bl[nt][1] = pk_tf32(x1 - __uint_as_float(bh[nt][1]));
+    }
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) {
+      const uint4 ahi = wfrag[((s * 4 + mt) * 2 + 0) * 32 + lane];
+      const uint4 alo = wfrag[((s * 4 + mt) * 2 + 1) * 32 + lane];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        pk_mma_tf32(d[mt][nt], alo, bh[nt][0], bh[nt][1]);  // small terms first
+        pk_mma_tf32(d[mt][nt], ahi, bl[nt][0], bl[nt][1]);
+        pk_mma_tf32(d[mt][nt], ahi, bh[nt][0], bh[nt][1]);
+      }
+    }
+  }
+}
+
 // ---- shared-memory plan ---------------------------------------------------------------------------
 struct PkSmemPlan {
   unsigned tail;         // prepared floats from lay.b[0] to lay.total (biases, hidden weights, head)
@@ -232,11 +315,12 @@ struct PkSmemPlan {
   unsigned warp_stride;
   unsigned zero_tile;    // block-wide tile of zeros: source of the TMA zero fill
   unsigned zero_bytes;
+  unsigned wfrag;        // tensor-path weight fragments of the hidden layers (PK_TC_WFRAG_BYTES each), or unused
   unsigned total;
 };
 
 __host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, int nwarps, bool with_mlp,
-                                                   bool zero_tile) {
+                                                   bool zero_tile, bool tc = false) {
   PkSmemPlan p;
   unsigned o = 0;
   p.tail = o;
@@ -244,12 +328,14 @@ __host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, 
   p.w1s = o;
   if (with_mlp) o += (unsigned)PK_N_STATE * lay.HP * 4u;
   p.warp_area = o;
-  p.warp_stride = PK_WARP_FIXED_BYTES + (with_mlp ? (unsigned)AT * lay.HP * 4u : 0u);
+  p.warp_stride = PK_WARP_FIXED_BYTES + (with_mlp ? (unsigned)AT * (tc ? (unsigned)PK_TC_HS : lay.HP) * 4u : 0u);
   o += p.warp_stride * nwarps;
   o = (o + 127u) & ~127u;
   p.zero_tile = o;
   p.zero_bytes = zero_tile ? ((((unsigned)lay.C * AT * 4u) + 15u) & ~15u) : 0u;
   o += p.zero_bytes;
+  p.wfrag = o;
+  if (tc) o += PK_TC_WFRAG_BYTES * (unsigned)(lay.n_layers - 1);
   p.total = o;
   return p;
 }
@@ -432,21 +518,13 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   const bool with_mlp = prep != nullptr;
   const int L = lay.C * A;  // floats per battle
   const bool use_tma = feat != nullptr && (zero_by_tma & 1) != 0;
-  const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp, use_tma);
+  const bool tc = CPL == 2 && with_mlp && (zero_by_tma & 2) != 0;  // hidden layers on the tensor path (64 channels)
+  const int HS = tc ? PK_TC_HS : HP;                                // row stride of hbuf
+  const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp, use_tma, tc);
 
   unsigned long long* tr = sel.trace;
   const int tslot = blockIdx.x * nwarps + warp;
   pk_trace(tr, tslot, 0);
-  if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
-  const float* zero_tile = nullptr;
-  if (use_tma) {
-    float4* z = reinterpret_cast<float4*>(smem + plan.zero_tile);
-    for (int i = threadIdx.x; i < (int)(plan.zero_bytes >> 4); i += blockDim.x) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    pk_fence_proxy_async_smem();  // the async proxy (TMA) reads what the generic proxy just wrote
-    zero_tile = reinterpret_cast<const float*>(z);
-  }
-  if (with_mlp || use_tma) __syncthreads();
-  pk_trace(tr, tslot, 1);
 
   unsigned char* wa = smem + plan.warp_area + warp * plan.warp_stride;
   uint4* rec = reinterpret_cast<uint4*>(wa);
@@ -458,23 +536,36 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   const float* s_w1s = reinterpret_cast<const float*>(smem + plan.w1s);
   const float* w1t = prep + lay.w1t;
   const int zero_row = lay.C;
-  float b1r[CPL];
-  if (with_mlp) pk_lds_vec<CPL>(s_tail, lane, b1r);  // lay.b[0] is the start of the tail
 
-  // battles are dealt round-robin over every warp of the grid
+  // battles are dealt round-robin over every warp of the grid.  The first record is requested before the
+  // prologue and parsed while the weight staging loads are in flight (nothing in the parse needs them).
   const long long stride = (long long)gridDim.x * nwarps;
   long long b = (long long)warp * gridDim.x + blockIdx.x;
   uint4 cur = make_uint4(0u, 0u, 0u, 0u);
   if (b < B && lane < 9) cur = __ldg(packed + b * 9 + lane);
 
-  for (; b < B; b += stride) {
-    __syncwarp();  // the previous battle's readers of rec / sv / idx are done
+  if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
+  const uint4* wfrag = reinterpret_cast<const uint4*>(smem + plan.wfrag);
+  if constexpr (CPL == 2) {
+    if (tc)
+      for (int l = 1; l < lay.n_layers; ++l)
+        pk_tc_build_wfrag(prep + lay.wl[l], reinterpret_cast<uint4*>(smem + plan.wfrag) + (l - 1) * 2048);
+  }
+  const float* zero_tile = nullptr;
+  if (use_tma) {
+    float4* z = reinterpret_cast<float4*>(smem + plan.zero_tile);
+    for (int i = threadIdx.x; i < (int)(plan.zero_bytes >> 4); i += blockDim.x) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    pk_fence_proxy_async_smem();  // the async proxy (TMA) reads what the generic proxy just wrote
+    zero_tile = reinterpret_cast<const float*>(z);
+  }
+
+  // record -> smem, next record requested, state values and gather rows derived (the warp's own scratch only)
+  auto take_and_parse = [&]() {
     if (lane < 9) rec[lane] = cur;
     if (b + stride < B && lane < 9) cur = __ldg(packed + (b + stride) * 9 + lane);  // prefetch, consumed next turn
     __syncwarp();
-    pk_trace(tr, tslot, 2);
-    const int n_act = min((int)r[PK_OFF_NACT], A);
-    if (mask != nullptr && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;  // feature_extractor.py:50-51
+    const int na = min((int)r[PK_OFF_NACT], A);
+    if (mask != nullptr && lane < A) mask[b * A + lane] = lane < na ? 1 : 0;  // feature_extractor.py:50-51
     sv[lane] = pk_state_feature(r, lane);
     sv[lane + 32] = pk_state_feature(r, lane + 32);
 #pragma unroll
@@ -482,12 +573,26 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
       const int e = lane + 32 * it;
       if (e < 8 * A) {
         const int c = e >> 3;
-        const int row = c < n_act ? pk_choice_row(r, c, e & 7) : -1;
+        const int row = c < na ? pk_choice_row(r, c, e & 7) : -1;
         idx[e] = row < 0 ? zero_row : row;
       }
     }
     __syncwarp();
-    pk_trace(tr, tslot, 3);
+  };
+  pk_trace(tr, tslot, 1);
+  if (b < B) take_and_parse();
+  pk_trace(tr, tslot, 2);
+  if (with_mlp || use_tma) __syncthreads();
+  pk_trace(tr, tslot, 3);
+  float b1r[CPL];
+  if (with_mlp) pk_lds_vec<CPL>(s_tail, lane, b1r);  // lay.b[0] is the start of the tail
+
+  for (bool first = true; b < B; b += stride, first = false) {
+    if (!first) {
+      __syncwarp();  // the previous battle's readers of rec / sv / idx are done
+      take_and_parse();
+    }
+    const int n_act = min((int)r[PK_OFF_NACT], A);
 
     float* gfeat = feat != nullptr ? feat + (size_t)b * L : nullptr;
     if (gfeat != nullptr) {
@@ -574,7 +679,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
         const float s45 = gc[4][i] + gc[5][i], s67 = gc[6][i] + gc[7][i];
         hc[i] = fmaxf(base[i] + ((s01 + s23) + (s45 + s67)), 0.0f);
       }
-      pk_sts_vec<CPL>(hbuf + c * HP, lane, hc);
+      pk_sts_vec<CPL>(hbuf + c * HS, lane, hc);
       if (c + 1 < AT) {
 #pragma unroll
         for (int t = 0; t < 8; ++t)
@@ -586,7 +691,57 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
     pk_trace(tr, tslot, 6);
     // ---- hidden layers (input in hbuf) + head ----------------------------------------------------------
     float qv[AT];
-    {
+    bool q_done = false;
+    if constexpr (CPL == 2) {
+      if (tc) {
+        constexpr int NT = (A + 7) / 8;
+        const unsigned tb = lay.b[0];
+        const int g4 = lane >> 2, t4 = lane & 3;
+        float d[4][NT][4];
+        for (int l = 1; l < lay.n_layers; ++l) {
+          pk_hidden_tc<A>(wfrag + (l - 1) * 2048, s_tail + (lay.b[l] - tb), hbuf, d, lane);
+          if (l + 1 < lay.n_layers) {  // relu -> hbuf[column][channel] for the next layer
+            __syncwarp();
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+              for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const int col = 8 * nt + 2 * t4 + (i & 1), ch = 16 * mt + g4 + ((i & 2) ? 8 : 0);
+                  if (col < A) hbuf[col * PK_TC_HS + ch] = fmaxf(d[mt][nt][i], 0.0f);
+                }
+            __syncwarp();
+          }
+        }
+        const float* wo = s_tail + (lay.wout - tb);
+        const float bo = s_tail[lay.bout - tb];
+        float p[NT][2];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) p[nt][0] = p[nt][1] = 0.0f;
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+          const float w0 = wo[16 * mt + g4], w1 = wo[16 * mt + g4 + 8];
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt) {
+            p[nt][0] = fmaf(w0, fmaxf(d[mt][nt][0], 0.0f), p[nt][0]);
+            p[nt][1] = fmaf(w0, fmaxf(d[mt][nt][1], 0.0f), p[nt][1]);
+            p[nt][0] = fmaf(w1, fmaxf(d[mt][nt][2], 0.0f), p[nt][0]);
+            p[nt][1] = fmaf(w1, fmaxf(d[mt][nt][3], 0.0f), p[nt][1]);
+          }
+        }
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int o = 4; o < 32; o <<= 1) p[nt][i] += __shfl_xor_sync(0xffffffffu, p[nt][i], o);
+#pragma unroll
+        for (int c = 0; c < AT; ++c) qv[c] = __shfl_sync(0xffffffffu, p[c >> 3][c & 1], (c & 7) >> 1) + bo;
+        q_done = true;
+      }
+    }
+    if (!q_done) {
       const unsigned tb = lay.b[0];
       float acc[AT][CPL];
       for (int l = 1; l < lay.n_layers; ++l) {

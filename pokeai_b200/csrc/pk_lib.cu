@@ -45,6 +45,7 @@ struct PkGlobal {
   int decide_warps = 16;
   int encode_warps = 16;
   int decide_pair = 1;
+  int hidden_tc = 0;
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
@@ -90,6 +91,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.encode_warps = env_int("PK_ENCODE_WARPS", 16, 1, 16);
   g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
+  g.hidden_tc = env_int("PK_HIDDEN_TC", 0, 0, 1);  // 64-channel hidden layers on the 3xTF32 mma.sync path (measured: no gain)
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   return PK_OK;
 }
@@ -101,6 +103,10 @@ extern "C" int pk_init(const pk_tables* t, int device) {
 
 extern "C" int pk_debug_set_trace(unsigned long long* device_buffer) {
   g.trace = device_buffer;
+  return PK_OK;
+}
+extern "C" int pk_debug_set_hidden_tc(int on) {
+  g.hidden_tc = on ? 1 : 0;
   return PK_OK;
 }
 extern "C" int pk_debug_set_pairing(int mode) {
@@ -256,10 +262,12 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   }
   int nwarps = with_mlp ? g.decide_warps : g.encode_warps;
   if (nwarps > 16) nwarps = 16;  // the 128-channel instantiation needs > 64 registers per thread
-  PkSmemPlan plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma);
+  bool tc = with_mlp && lay.HP == 64 && n_layers >= 2 && g.hidden_tc != 0;
+  if (tc && pk_smem_plan(lay, A, nwarps, with_mlp, use_tma, true).total > (unsigned)g.max_smem) tc = false;
+  PkSmemPlan plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma, tc);
   while (plan.total > (unsigned)g.max_smem && nwarps > 1) {  // drop warps until the plan fits
     --nwarps;
-    plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma);
+    plan = pk_smem_plan(lay, A, nwarps, with_mlp, use_tma, tc);
   }
   if (plan.total > (unsigned)g.max_smem)
     return pk_fail(PK_ERR_UNSUPPORTED,
@@ -272,7 +280,8 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
     int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                         \
     if (rc_) return rc_;                                                                                      \
     pk_decide_kernel<C_, A_, 512><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask,    \
-                                                                         q, action, ps, use_tma ? 1 : 0);     \
+                                                                         q, action, ps,                       \
+                                                                         (use_tma ? 1 : 0) | (tc ? 2 : 0));   \
   }
 #define PK_LAUNCH_DECIDE_A(C_)                                        \
   switch (A) {                                                        \

@@ -207,6 +207,40 @@ def test_paired_and_single_kernels_agree_with_oracle(tables, dev, ps, nl, H, B):
         N.check(N.lib().pk_debug_set_pairing(1))
 
 
+@pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 64, 4096), (6, 3, 64, 513), (3, 2, 48, 200), (1, 4, 64, 65), (6, 2, 33, 100)])
+def test_tensor_path_hidden_layer_matches_fp32_oracle(tables, dev, ps, nl, H, B):
+    """the 64-channel hidden layers run on mma.sync tf32 with a 3-term hi/lo split (pk_hidden_tc); Q must stay inside
+    the same fp32 tolerance as the FFMA path, features / masks bit-exact, and the two paths must agree closely"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import _native as N, ops
+    from pokeai_b200.packed import synth_packed
+    A = 4 + ps - 1
+    rec = synth_packed(B, seed=11 * B + H, party_size=ps, kind="ragged", tables=tables)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=H + 3 * nl)
+    fo, mo = packed_oracle.encode(rec, ps, tables)
+    with torch.no_grad():
+        qo = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    prepared, _, _, _ = ops.prepare_weights(sd, dev)
+    qs = {}
+    try:
+        N.check(N.lib().pk_debug_set_pairing(0))
+        for on in (1, 0):
+            N.check(N.lib().pk_debug_set_hidden_tc(on))
+            for mat in (True, False):
+                f, m, q, a = ops.decide(_to_dev(rec, dev), A, prepared, nl, H, materialise=mat)
+                qg = q.cpu().numpy()
+                np.testing.assert_allclose(qg, qo, rtol=Q_RTOL, atol=Q_ATOL, err_msg=f"hidden_tc={on} mat={mat}")
+                assert np.array_equal(m.cpu().numpy(), mo)
+                assert np.array_equal(a.cpu().numpy(), ref_port.masked_argmax(qg, mo))
+                if mat:
+                    assert np.array_equal(bits(f.cpu().numpy()), bits(fo))
+                qs[(on, mat)] = qg
+    finally:
+        N.check(N.lib().pk_debug_set_hidden_tc(0))
+        N.check(N.lib().pk_debug_set_pairing(1))
+    assert np.abs(qs[(1, True)] - qs[(0, True)]).max() < 5e-6
+
+
 def test_dense_forward_on_arbitrary_dense_input(tables, dev):
     """_calc_q_vector_batch accepts any float tensor, not only one-hot features"""
     from oracle import ref_port

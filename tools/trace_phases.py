@@ -21,7 +21,7 @@ torch.manual_seed(0)
 model = MLPModel((617, A), A).eval()
 prepared = model.prepared(dev)
 feat = torch.empty((B, 617, A), dtype=torch.float32, device=dev)
-names = ["start->prologue done", "->record in smem", "->parsed", "->features issued", "->state part", "->gathers",
+names = ["start->staging issued", "->first record parsed", "->prologue barrier", "->features issued", "->state part", "->gathers",
          "->hidden+head", "->select+stores", "->pokes done"]
 for mat in (True, False):
     for _ in range(3):
