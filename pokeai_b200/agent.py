@@ -70,6 +70,22 @@ class Agent:
         """Observations (objects or packed records) -> (q (B, A) float32 with -inf NOT applied,
         action (B,) int32).  Views of pinned buffers, valid until the next call."""
         n = len(obs_list)
+        m = self._model
+        from .wide import WideRunner, is_wide
+        if hasattr(m, "n_channels") and is_wide(m.n_channels):
+            # wide network (e.g. 4 x 2048): tensor-core path (pokeai_b200/wide.py), same semantics
+            from .ops import SelectSpec
+            fe = self._feature_extractor
+            if getattr(self, "_wide", None) is None or self._wide.model is not m:
+                self._wide = WideRunner(m, fe.output_dim, fe.session(1).device)
+            rec = fe.pack(obs_list)
+            spec = None
+            if mode != N.PK_SELECT_ARGMAX:
+                dev = self._wide.device
+                ue = torch.from_numpy(np.asarray(u_explore, dtype=np.float32)).to(dev) if u_explore is not None else None
+                up = torch.from_numpy(np.asarray(u_pick, dtype=np.float32)).to(dev)
+                spec = SelectSpec(mode, eps, temperature, ue, up)
+            return self._wide.decide(rec, spec)
         s = self._session(n)
         self._feature_extractor.pack(obs_list, out=s.packed)
         if mode == N.PK_SELECT_EPSGREEDY:

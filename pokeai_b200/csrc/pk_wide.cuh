@@ -122,6 +122,7 @@ struct PkwGemmArgs {
   const __nv_bfloat16* relu_mask;  // (M, N) bf16 or null: out = mask > 0 ? acc : 0 (backward through a ReLU)
   int M, N, K;            // N % 32 == 0; tails in M, N (to 256) and K (to 64) are zero-filled by TMA
   int relu;
+  int ksplit;             // >= 1: the contraction is cut into ksplit ranges; range s writes out_f32 + s * M * N
 };
 
 // MN == 0:  Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
@@ -144,7 +145,9 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_mblk = (g.M + PKW_BM - 1) / PKW_BM, n_nblk = (g.N + PKW_BN - 1) / PKW_BN,
             n_kblk = (g.K + PKW_BK - 1) / PKW_BK;
-  const int n_tiles = n_mblk * n_nblk;
+  const int n_mn = n_mblk * n_nblk;
+  const int n_tiles = n_mn * g.ksplit;                      // tile = split * n_mn + mb * n_nblk + nb
+  const int kps = (n_kblk + g.ksplit - 1) / g.ksplit;       // k-blocks per split
 
   if (threadIdx.x == 0) {
     pkw_prefetch_map(&map_a);
@@ -170,8 +173,10 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     int s = 0;
     uint32_t ph = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-      const int mb = tile / n_nblk, nb = tile - mb * n_nblk;
-      for (int kb = 0; kb < n_kblk; ++kb) {
+      const int sp = tile / n_mn, mn = tile - sp * n_mn;
+      const int mb = mn / n_nblk, nb = mn - mb * n_nblk;
+      const int kb0 = sp * kps, kb1 = min(n_kblk, kb0 + kps);
+      for (int kb = kb0; kb < kb1; ++kb) {
         pk_mbar_wait(empty + s, ph ^ 1u);
         pk_mbar_expect_tx(full + s, PKW_STAGE_BYTES);
         unsigned char* sa = tiles + s * PKW_STAGE_BYTES;
@@ -204,7 +209,9 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       pk_mbar_wait(tempty + as, aph ^ 1u);  // the epilogue has drained this accumulator
       pkw_tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * PKW_BN);
-      for (int kb = 0; kb < n_kblk; ++kb) {
+      const int sp = tile / n_mn;
+      const int kb0 = sp * kps, kb1 = min(n_kblk, kb0 + kps);
+      for (int kb = kb0; kb < kb1; ++kb) {
         pk_mbar_wait(full + s, ph);
         pkw_tc_fence_after();
         const uint32_t sa = pk_smem_u32(tiles + s * PKW_STAGE_BYTES);
@@ -215,7 +222,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         constexpr uint64_t kstep = MN ? 128u : 2u;
 #pragma unroll
         for (int k = 0; k < PKW_BK / 16; ++k)
-          pkw_mma(d_tmem, adesc + kstep * (uint64_t)k, bdesc + kstep * (uint64_t)k, idesc, (kb | k) != 0 ? 1u : 0u);
+          pkw_mma(d_tmem, adesc + kstep * (uint64_t)k, bdesc + kstep * (uint64_t)k, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
         pkw_mma_commit(empty + s);  // frees the stage once these MMAs have read it
         if (++s == PKW_STAGES) {
           s = 0;
@@ -229,7 +236,9 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     const int quarter = warp & 3;  // a warp may only touch TMEM lanes 32 * (warp % 4) .. + 31
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const int mb = tile / n_nblk, nb = tile - mb * n_nblk;
+      const int sp = tile / n_mn, mn = tile - sp * n_mn;
+      const int mb = mn / n_nblk, nb = mn - mb * n_nblk;
+      float* const out_f32 = g.out_f32 != nullptr ? g.out_f32 + (size_t)sp * g.M * g.N : nullptr;
       const int as = it & 1;
       const uint32_t aph = (uint32_t)(it >> 1) & 1u;
       pk_mbar_wait(tfull + as, aph);
@@ -291,8 +300,8 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               dst[j >> 3] = o;
             }
           }
-          if (g.out_f32 != nullptr) {
-            float4* dst = reinterpret_cast<float4*>(g.out_f32 + (size_t)row * g.N + n0);
+          if (out_f32 != nullptr) {
+            float4* dst = reinterpret_cast<float4*>(out_f32 + (size_t)row * g.N + n0);
 #pragma unroll
             for (int j = 0; j < 32; j += 4) dst[j >> 2] = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
           }
@@ -524,4 +533,14 @@ __global__ void pk_wide_compact_kernel(const float* __restrict__ src, float* __r
   if (i >= (long long)rows * cols) return;
   const int r = (int)(i / cols), c = (int)(i - (long long)r * cols);
   dst[i] = src[(size_t)r * cols_pad + c];
+}
+// out (rows, cols) = sum over s (in order) of partial[s] (rows, cols_pad): split-K reduction + drop of the K padding
+__global__ void pk_wide_splitk_reduce_kernel(const float* __restrict__ partial, int nsplit, float* __restrict__ dst,
+                                             int rows, int cols, int cols_pad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)rows * cols) return;
+  const int r = (int)(i / cols), c = (int)(i - (long long)r * cols);
+  float a = 0.0f;
+  for (int sp = 0; sp < nsplit; ++sp) a += partial[((size_t)sp * rows + r) * cols_pad + c];
+  dst[i] = a;
 }

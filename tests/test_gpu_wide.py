@@ -191,3 +191,24 @@ def test_wide_backward_matches_oracle(tables, dev, ps, nl, H, B):
     # bit-reproducible: a second backward gives the same bits
     grad2 = wide.train_backward(prepared, nl, H, B, A, ws, torch.from_numpy(dq).to(dev))
     assert torch.equal(grad, grad2)
+
+
+def test_agent_dispatches_wide_models(tables, dev):
+    """AgentVal.act_batch with a wide MLPModel goes through the tensor-core path and returns the masked argmax"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200.agent import AgentVal
+    from pokeai_b200.feature_extractor import FeatureExtractor
+    from pokeai_b200.mlp_model import MLPModel
+    from pokeai_b200.packed import synth_packed
+    fe = FeatureExtractor(6, device=dev)
+    torch.manual_seed(2)
+    model = MLPModel(fe.input_shape, fe.output_dim, n_layers=2, n_channels=256).eval()
+    rec = synth_packed(64, seed=8, party_size=6, kind="ragged", tables=tables)
+    agent = AgentVal(model, fe)
+    q, a = agent.q_and_action_batch(rec)
+    fo, mo = packed_oracle.encode(rec, 6, tables)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        q32 = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    np.testing.assert_allclose(q, q32, rtol=0, atol=2e-2)
+    assert np.array_equal(agent.act_batch(rec), ref_port.masked_argmax(q, mo))
