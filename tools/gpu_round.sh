@@ -18,7 +18,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 echo "ncu launches rc=$?"
 echo "== ncu full"
 timeout 300 python tools/prof_decide.py > $OUT/plain_prof_$TAG.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:pk_decide_kernel -s 6 -c 3 -f -o $OUT/prof_$TAG \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:pk_decide -s 6 -c 3 -f -o $OUT/prof_$TAG \
     python tools/prof_decide.py > $OUT/ncu_full_$TAG.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT

@@ -48,7 +48,7 @@ if rep.exists():
                       r"smsp__inst_executed_op_tma_st.sum$|sm__cycles_elapsed.avg$|"
                       r"smsp__average_warps_issue_stalled_(long_scoreboard|short_scoreboard|wait|barrier|mio_throttle|lg_throttle|math_pipe_throttle|not_selected)_per_issue_active.ratio)")
     with open(P / f"{rnd}_ncu_full_raw.txt", "w") as f:
-        f.write(f"# ncu --set full --clock-control none --import-source on -k regex:pk_decide_kernel -s 6 -c 3  python tools/prof_decide.py\n")
+        f.write(f"# ncu --set full --clock-control none --import-source on -k regex:pk_decide -s 6 -c 3  python tools/prof_decide.py\n")
         f.write("# columns: launch 1 = pk_encode (features+mask only), 2 = pk_decide with features, 3 = pk_decide without features; B = 4096\n")
         for i, h in enumerate(hdr):
             if keep.search(h):
