@@ -506,7 +506,7 @@ __device__ __forceinline__ void pk_trace(unsigned long long* tr, int slot, int p
   }
 }
 
-template <int CPL, int A, int MAXT>
+template <int CPL, int A, int MAXT, bool TC = false>
 __global__ void __launch_bounds__(MAXT, 1)
 pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restrict__ prep, PkLayout lay,
                  float* __restrict__ feat, int* __restrict__ mask, float* __restrict__ q,
@@ -518,7 +518,8 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   const bool with_mlp = prep != nullptr;
   const int L = lay.C * A;  // floats per battle
   const bool use_tma = feat != nullptr && (zero_by_tma & 1) != 0;
-  const bool tc = CPL == 2 && with_mlp && (zero_by_tma & 2) != 0;  // hidden layers on the tensor path (64 channels)
+  static_assert(!TC || CPL == 2, "the tensor-path hidden layer is written for 64 channels");
+  constexpr bool tc = TC;  // hidden layers on the warp-level tensor path (compile-time: keeps the default kernel lean)
   const int HS = tc ? PK_TC_HS : HP;                                // row stride of hbuf
   const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp, use_tma, tc);
 
@@ -546,8 +547,8 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
 
   if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
   const uint4* wfrag = reinterpret_cast<const uint4*>(smem + plan.wfrag);
-  if constexpr (CPL == 2) {
-    if (tc)
+  if constexpr (TC) {
+    if (with_mlp)
       for (int l = 1; l < lay.n_layers; ++l)
         pk_tc_build_wfrag(prep + lay.wl[l], reinterpret_cast<uint4*>(smem + plan.wfrag) + (l - 1) * 2048);
   }
@@ -692,8 +693,8 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
     // ---- hidden layers (input in hbuf) + head ----------------------------------------------------------
     float qv[AT];
     bool q_done = false;
-    if constexpr (CPL == 2) {
-      if (tc) {
+    if constexpr (TC) {
+      {
         constexpr int NT = (A + 7) / 8;
         const unsigned tb = lay.b[0];
         const int g4 = lane >> 2, t4 = lane & 3;

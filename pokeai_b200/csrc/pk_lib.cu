@@ -277,11 +277,19 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   if (grid > g.sm_count * g.ctas_per_sm) grid = g.sm_count * g.ctas_per_sm;
 #define PK_LAUNCH_DECIDE(C_, A_)                                                                              \
   {                                                                                                           \
+    if constexpr (C_ == 2) {                                                                                  \
+      if (tc) {                                                                                               \
+        int rc_ = pk_set_smem(pk_decide_kernel<2, A_, 512, true>, plan.total);                                \
+        if (rc_) return rc_;                                                                                  \
+        pk_decide_kernel<2, A_, 512, true><<<grid, nwarps * 32, plan.total, st>>>(                            \
+            pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0);                                \
+        break;                                                                                                \
+      }                                                                                                       \
+    }                                                                                                         \
     int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                         \
     if (rc_) return rc_;                                                                                      \
     pk_decide_kernel<C_, A_, 512><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask,    \
-                                                                         q, action, ps,                       \
-                                                                         (use_tma ? 1 : 0) | (tc ? 2 : 0));   \
+                                                                         q, action, ps, use_tma ? 1 : 0);     \
   }
 #define PK_LAUNCH_DECIDE_A(C_)                                        \
   switch (A) {                                                        \
