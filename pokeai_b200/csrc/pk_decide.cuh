@@ -316,6 +316,7 @@ struct PkSmemPlan {
   unsigned zero_tile;    // block-wide tile of zeros: source of the TMA zero fill
   unsigned zero_bytes;
   unsigned wfrag;        // tensor-path weight fragments of the hidden layers (PK_TC_WFRAG_BYTES each), or unused
+  unsigned mbar;         // one mbarrier: completion of the TMA bulk loads that stage the weights
   unsigned total;
 };
 
@@ -336,6 +337,9 @@ __host__ __device__ inline PkSmemPlan pk_smem_plan(const PkLayout& lay, int AT, 
   o += p.zero_bytes;
   p.wfrag = o;
   if (tc) o += PK_TC_WFRAG_BYTES * (unsigned)(lay.n_layers - 1);
+  o = (o + 15u) & ~15u;
+  p.mbar = o;
+  o += 16u;
   p.total = o;
   return p;
 }
@@ -545,7 +549,18 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   uint4 cur = make_uint4(0u, 0u, 0u, 0u);
   if (b < B && lane < 9) cur = __ldg(packed + b * 9 + lane);
 
-  if (with_mlp) pk_stage_weights(smem, plan, prep, lay);
+  // the network's small tensors (biases, hidden matrices, head; the 50 state rows of W0^T: 30 KB for 2 x 64) are
+  // staged by two TMA bulk loads issued by one thread; everybody else goes on to the zero tile and the first
+  // record, and waits on the mbarrier only after the prologue barrier
+  uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + plan.mbar);
+  if (with_mlp && threadIdx.x == 0) {
+    const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
+    pk_mbar_init(wbar, 1);
+    pk_fence_mbar_init();
+    pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
+    pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
+    pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
+  }
   const uint4* wfrag = reinterpret_cast<const uint4*>(smem + plan.wfrag);
   if constexpr (TC) {
     if (with_mlp)
@@ -584,6 +599,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   if (b < B) take_and_parse();
   pk_trace(tr, tslot, 2);
   if (with_mlp || use_tma) __syncthreads();
+  if (with_mlp) pk_mbar_wait(wbar, 0);  // the staged weights have landed (async proxy -> visible after the wait)
   pk_trace(tr, tslot, 3);
   float b1r[CPL];
   if (with_mlp) pk_lds_vec<CPL>(s_tail, lane, b1r);  // lay.b[0] is the start of the tail

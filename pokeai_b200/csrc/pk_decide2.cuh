@@ -32,6 +32,10 @@ __host__ __device__ inline PkSmemPlan pk2_smem_plan(const PkLayout& lay, int A, 
   p.zero_tile = o;
   p.zero_bytes = zero_tile ? ((((unsigned)lay.C * A * 4u) + 15u) & ~15u) : 0u;
   o += p.zero_bytes;
+  p.wfrag = o;
+  o = (o + 15u) & ~15u;
+  p.mbar = o;
+  o += 16u;
   p.total = o;
   return p;
 }
@@ -136,7 +140,15 @@ pk_decide2_kernel(const uint4* __restrict__ packed, int B, const float* __restri
   unsigned long long* tr = sel.trace;
   const int tslot = blockIdx.x * nwarps + warp;
   pk_trace(tr, tslot, 0);
-  pk_stage_weights(smem, plan, prep, lay);
+  uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + plan.mbar);
+  if (threadIdx.x == 0) {  // weights staged by two TMA bulk loads, waited for after the prologue barrier
+    const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
+    pk_mbar_init(wbar, 1);
+    pk_fence_mbar_init();
+    pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
+    pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
+    pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
+  }
   const float* zero_tile = nullptr;
   if (use_tma) {
     float4* z = reinterpret_cast<float4*>(smem + plan.zero_tile);
@@ -163,7 +175,8 @@ pk_decide2_kernel(const uint4* __restrict__ packed, int B, const float* __restri
   long long p = (long long)warp * gridDim.x + blockIdx.x;
   uint4 cur = make_uint4(0u, 0u, 0u, 0u);
   if (p < NP && lane < 18 && p * 18 + lane < n16) cur = __ldg(packed + p * 18 + lane);
-  __syncthreads();  // staged weights and the zero tile are visible
+  __syncthreads();  // the mbarrier is initialised and the zero tile is visible
+  pk_mbar_wait(wbar, 0);  // staged weights have landed
   pk_trace(tr, tslot, 1);
 
   const uint8_t* r_own = reinterpret_cast<const uint8_t*>(rec) + PK_WARP_REC_BYTES * half;
