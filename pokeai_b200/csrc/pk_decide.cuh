@@ -224,6 +224,31 @@ __device__ __forceinline__ void pk_fma_vec(float (&acc)[CPL], const float (&w)[C
   }
 }
 
+// the 8 row slots of one action column: eight independent loads of W0^T row slices.  Empty slots and illegal
+// columns carry zero_row (all zeros): they are not fetched (warp-uniform predicate) -- the gathers are bound by L1
+// bandwidth (256 B per row and warp), and a typical state uses 47 of its 72 slots.
+template <int CPL>
+__device__ __forceinline__ void pk_gather_row(const float* __restrict__ w1t, int row, int zero_row, int HP, int lane,
+                                              float (&v)[CPL]) {
+#pragma unroll
+  for (int i = 0; i < CPL; ++i) v[i] = 0.0f;
+  if (row != zero_row) pk_ldg_vec<CPL>(w1t + (size_t)row * HP, lane, v);
+}
+template <int CPL>
+__device__ __forceinline__ void pk_gather_column(const float* __restrict__ w1t, const int* idx8, int zero_row, int HP,
+                                                 int lane, float (&g)[8][CPL]) {
+  const int4 ia = *reinterpret_cast<const int4*>(idx8);
+  const int4 ib = *reinterpret_cast<const int4*>(idx8 + 4);
+  pk_gather_row<CPL>(w1t, ia.x, zero_row, HP, lane, g[0]);
+  pk_gather_row<CPL>(w1t, ia.y, zero_row, HP, lane, g[1]);
+  pk_gather_row<CPL>(w1t, ia.z, zero_row, HP, lane, g[2]);
+  pk_gather_row<CPL>(w1t, ia.w, zero_row, HP, lane, g[3]);
+  pk_gather_row<CPL>(w1t, ib.x, zero_row, HP, lane, g[4]);
+  pk_gather_row<CPL>(w1t, ib.y, zero_row, HP, lane, g[5]);
+  pk_gather_row<CPL>(w1t, ib.z, zero_row, HP, lane, g[6]);
+  pk_gather_row<CPL>(w1t, ib.w, zero_row, HP, lane, g[7]);
+}
+
 // ---- hidden layer on the warp-level tensor path (64 channels): 3xTF32 split, fp32 accuracy --------------------
 // D (64 channels x <= 16 columns) = W (64 x 64) . h (64 x columns) with mma.sync.m16n8k8 tf32.  Every fp32 operand is
 // split x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and the product is hi*hi + lo*hi + hi*lo with fp32
@@ -629,6 +654,10 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
       continue;
     }
 
+    constexpr int GD = CPL <= 2 ? (AT < 4 ? AT : 4) : (AT < 2 ? AT : 2);  // gather ring depth (columns in flight)
+    float gr[GD][8][CPL];
+#pragma unroll
+    for (int c = 0; c < GD; ++c) pk_gather_column<CPL>(w1t, idx + 8 * c, zero_row, HP, lane, gr[c]);
     // ---- layer 0, state part: shared by every column of this battle (two chains for ILP) ----------
     float base[CPL], base2[CPL];
 #pragma unroll
@@ -660,49 +689,20 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
     for (int i = 0; i < CPL; ++i) base[i] += base2[i];
     pk_trace(tr, tslot, 5);
     // ---- layer 0, choice part: 8 row slots per column gathered from W1^T (absent slots and illegal columns
-    //      point at the all-zero row, so there is no branch); the loads of column c+1 are in flight while
-    //      column c is summed; relu(h) goes straight to the warp's hbuf --------------------------------------
-    float gc[8][CPL], gn[8][CPL];
-    {
-      const int4 ia = *reinterpret_cast<const int4*>(idx);
-      const int4 ib = *reinterpret_cast<const int4*>(idx + 4);
-      pk_ldg_vec<CPL>(w1t + (size_t)ia.x * HP, lane, gc[0]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ia.y * HP, lane, gc[1]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ia.z * HP, lane, gc[2]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ia.w * HP, lane, gc[3]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ib.x * HP, lane, gc[4]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ib.y * HP, lane, gc[5]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ib.z * HP, lane, gc[6]);
-      pk_ldg_vec<CPL>(w1t + (size_t)ib.w * HP, lane, gc[7]);
-    }
+    //      point at the all-zero row, so there is no branch).  The gathers miss L1 about half the time, so a ring of
+    //      GD columns (8 GD row loads) is kept in flight: the first GD columns were requested BEFORE the state part
+    //      above, column c + GD is requested when column c is summed; relu(h) goes straight to the warp's hbuf -------
 #pragma unroll
     for (int c = 0; c < AT; ++c) {
-      if (c + 1 < AT) {
-        const int4 ia = *reinterpret_cast<const int4*>(idx + 8 * (c + 1));
-        const int4 ib = *reinterpret_cast<const int4*>(idx + 8 * (c + 1) + 4);
-        pk_ldg_vec<CPL>(w1t + (size_t)ia.x * HP, lane, gn[0]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ia.y * HP, lane, gn[1]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ia.z * HP, lane, gn[2]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ia.w * HP, lane, gn[3]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ib.x * HP, lane, gn[4]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ib.y * HP, lane, gn[5]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ib.z * HP, lane, gn[6]);
-        pk_ldg_vec<CPL>(w1t + (size_t)ib.w * HP, lane, gn[7]);
-      }
       float hc[CPL];
 #pragma unroll
       for (int i = 0; i < CPL; ++i) {
-        const float s01 = gc[0][i] + gc[1][i], s23 = gc[2][i] + gc[3][i];
-        const float s45 = gc[4][i] + gc[5][i], s67 = gc[6][i] + gc[7][i];
+        const float s01 = gr[c % GD][0][i] + gr[c % GD][1][i], s23 = gr[c % GD][2][i] + gr[c % GD][3][i];
+        const float s45 = gr[c % GD][4][i] + gr[c % GD][5][i], s67 = gr[c % GD][6][i] + gr[c % GD][7][i];
         hc[i] = fmaxf(base[i] + ((s01 + s23) + (s45 + s67)), 0.0f);
       }
       pk_sts_vec<CPL>(hbuf + c * HS, lane, hc);
-      if (c + 1 < AT) {
-#pragma unroll
-        for (int t = 0; t < 8; ++t)
-#pragma unroll
-          for (int i = 0; i < CPL; ++i) gc[t][i] = gn[t][i];
-      }
+      if (c + GD < AT) pk_gather_column<CPL>(w1t, idx + 8 * (c + GD), zero_row, HP, lane, gr[c % GD]);
     }
     __syncwarp();
     pk_trace(tr, tslot, 6);
