@@ -267,12 +267,19 @@ PK_API int pk_gemm_bf16_tn(const void* a_km_bf16, const void* w_kn_bf16, float* 
  * pk_wide_train_forward keeps every layer's bf16 activations in the workspace and returns q (B,A); the caller
  * forms dq = d loss / d q (B*A fp32, zero for columns that carry no loss -- trainer.py:163 gathers the chosen one);
  * pk_wide_train_backward returns the flat fp32 gradient in state_dict order (pk_mlp_param_floats floats).
- * B*A must be a multiple of 8.  Gradients are bit-reproducible (no atomics). */
+ * Gradients are bit-reproducible (no atomics). */
 PK_API size_t pk_wide_train_workspace_bytes(int n_layers, int n_channels, int in_channels, int B, int A);
-PK_API int pk_wide_train_forward(const pk_obs* packed, int B, int A, const void* wide_prepared, int n_layers,
-                                 int n_channels, void* workspace, int32_t* mask, float* q, void* stream);
-PK_API int pk_wide_train_backward(const void* wide_prepared, int n_layers, int n_channels, int B, int A, void* workspace,
-                                  const float* dq, float* grad, void* stream);
+/* col_select == NULL: every action column is a row (q is (B,A), dq is (B*A,)).  col_select (B,) int32: only that
+ * column of each battle is evaluated (q and dq are (B,)) -- the gather(1, action) of trainer.py:163, 9x less work. */
+PK_API int pk_wide_train_forward(const pk_obs* packed, int B, int A, const int32_t* col_select, const void* wide_prepared,
+                                 int n_layers, int n_channels, void* workspace, int32_t* mask, float* q, void* stream);
+PK_API int pk_wide_train_backward(const void* wide_prepared, int n_layers, int n_channels, int B, int A, int chosen_only,
+                                  void* workspace, const float* dq, float* grad, void* stream);
+/* Double-DQN target y = r + gamma * Q_target(s', argmax_legal Q_online(s')) (0 for terminal), Huber loss (mean over
+ * n_global) and dq = clamp(q_sa - y, -1, 1) / n_global: trainer.py:163-187 for the wide path.  Fixed-order sums. */
+PK_API int pk_wide_dqn_dq(const float* q_sa, const float* q_next_online, const float* q_next_target,
+                          const int32_t* mask_next, const float* reward, const uint8_t* terminal, int n, int A,
+                          int n_global, float gamma, int double_dqn, float* dq, float* loss, void* stream);
 
 #ifdef __cplusplus
 }

@@ -327,7 +327,9 @@ __host__ __device__ inline unsigned pkw_enc_warp_bytes(int A, int kpad) {
 }
 __global__ void __launch_bounds__(PKW_ENC_WARPS * 32)
 pk_wide_encode_kernel(const uint4* __restrict__ packed, int B, int A, int C, int kpad, __nv_bfloat16* __restrict__ X,
-                      int* __restrict__ mask) {
+                      int* __restrict__ mask, const int* __restrict__ col_select) {
+  // col_select == null: A rows per battle (one per action column).  Otherwise ONE row per battle, the column
+  // col_select[b] (the chosen action of a transition: trainer.py:163 gathers only that column).
   extern __shared__ __align__(16) unsigned char enc_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned char* wa = enc_smem + warp * pkw_enc_warp_bytes(A, kpad);
@@ -336,7 +338,8 @@ pk_wide_encode_kernel(const uint4* __restrict__ packed, int B, int A, int C, int
   float* sv = reinterpret_cast<float*>(wa + PK_WARP_REC_BYTES);
   int* idx = reinterpret_cast<int*>(wa + PK_WARP_REC_BYTES + PK_WARP_SV_BYTES);
   __nv_bfloat16* rows = reinterpret_cast<__nv_bfloat16*>(wa + PK_WARP_FIXED_BYTES + 16u);  // [A][kpad]
-  const int n16 = A * kpad / 8;  // uint4 chunks of the battle's rows
+  const int RA = col_select != nullptr ? 1 : A;  // rows emitted per battle
+  const int n16 = RA * kpad / 8;                 // uint4 chunks of the battle's rows
   const __nv_bfloat16 one = __float2bfloat16_rn(1.0f);
   for (long long b = (long long)blockIdx.x * PKW_ENC_WARPS + warp; b < B; b += (long long)gridDim.x * PKW_ENC_WARPS) {
     __syncwarp();
@@ -358,20 +361,22 @@ pk_wide_encode_kernel(const uint4* __restrict__ packed, int B, int A, int C, int
       }
     }
     __syncwarp();
+    const int sel = col_select != nullptr ? __ldg(col_select + b) : -1;
     for (int k = lane; k < PK_N_STATE; k += 32) {  // state rows fill every column (feature_extractor.py:48)
       const __nv_bfloat16 v = __float2bfloat16_rn(sv[k]);
-      for (int c = 0; c < A; ++c) rows[c * kpad + k] = v;
+      for (int c = 0; c < RA; ++c) rows[c * kpad + k] = v;
     }
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
       const int e = lane + 32 * it;
       if (e < 8 * A) {
         const int row = idx[e];
-        if (row != C) rows[(e >> 3) * kpad + row] = one;
+        const int c = e >> 3;
+        if (row != C && (sel < 0 || c == sel)) rows[(sel < 0 ? c : 0) * kpad + row] = one;
       }
     }
     __syncwarp();
-    uint4* dst = reinterpret_cast<uint4*>(X + (size_t)b * A * kpad);
+    uint4* dst = reinterpret_cast<uint4*>(X + (size_t)b * RA * kpad);
     for (int i = lane; i < n16; i += 32) dst[i] = r16[i];
   }
 }
@@ -543,4 +548,45 @@ __global__ void pk_wide_splitk_reduce_kernel(const float* __restrict__ partial, 
   float a = 0.0f;
   for (int sp = 0; sp < nsplit; ++sp) a += partial[((size_t)sp * rows + r) * cols_pad + c];
   dst[i] = a;
+}
+
+// ---- Double-DQN target, Huber loss and d loss / d q for the wide network (trainer.py:163-187) -----------------
+// q_sa (n,): Q of the chosen column; q_no / q_nt (n, A): online / target Q of next_state; mask_next (n, A).
+// dq[i] = clamp(q_sa - y, -1, 1) / n_global (derivative of smooth_l1 with beta = 1, mean over the GLOBAL batch);
+// loss[0] = sum_i huber_i / n_global, summed in a fixed order by one block.
+__global__ void __launch_bounds__(1024)
+pk_wide_dqn_dq_kernel(const float* __restrict__ q_sa, const float* __restrict__ q_no, const float* __restrict__ q_nt,
+                      const int* __restrict__ mask_next, const float* __restrict__ reward,
+                      const unsigned char* __restrict__ terminal, int n, int A, int n_global, float gamma, int double_dqn,
+                      float* __restrict__ dq, float* __restrict__ loss) {
+  __shared__ float sh[1024];
+  float acc = 0.0f;
+  for (int i = threadIdx.x; i < n; i += 1024) {
+    float v = 0.0f;
+    if (!terminal[i]) {
+      float best = -CUDART_INF_F;
+      int bi = 0;
+      const float* sel = double_dqn ? q_no : q_nt;  // :171-182
+      for (int c = 0; c < A; ++c) {
+        const float x = mask_next[(size_t)i * A + c] != 0 ? sel[(size_t)i * A + c] : -CUDART_INF_F;
+        if (x > best) {
+          best = x;
+          bi = c;
+        }
+      }
+      v = double_dqn ? q_nt[(size_t)i * A + bi] : best;
+    }
+    const float y = fmaf(v, gamma, reward[i]);  // :184
+    const float d = q_sa[i] - y;
+    const float ad = fabsf(d);
+    acc += ad < 1.0f ? 0.5f * d * d : ad - 0.5f;  // F.smooth_l1_loss, :187
+    dq[i] = fminf(fmaxf(d, -1.0f), 1.0f) / (float)n_global;
+  }
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) loss[0] = sh[0] / (float)n_global;
 }

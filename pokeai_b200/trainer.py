@@ -144,9 +144,16 @@ class Trainer:
         m = self.model
         self._nl, self._H, self._C = m.n_layers, m.n_channels, m.in_channels
         lib = N.lib()
-        n_prep = lib.pk_mlp_prepared_floats(self._nl, self._H, self._C)
-        self._prepared = torch.zeros(n_prep, dtype=torch.float32, device=self.device)
-        self._prepared_target = torch.zeros(n_prep, dtype=torch.float32, device=self.device)
+        from .wide import is_wide
+        self._wide = is_wide(self._H)  # 4 x 2048 and the like: tensor-core path (pokeai_b200/wide.py)
+        if self._wide:
+            n_prep = lib.pk_wide_prepared_bytes(self._nl, self._H, self._C)
+            self._prepared = torch.zeros(n_prep, dtype=torch.uint8, device=self.device)
+            self._prepared_target = torch.zeros(n_prep, dtype=torch.uint8, device=self.device)
+        else:
+            n_prep = lib.pk_mlp_prepared_floats(self._nl, self._H, self._C)
+            self._prepared = torch.zeros(n_prep, dtype=torch.float32, device=self.device)
+            self._prepared_target = torch.zeros(n_prep, dtype=torch.float32, device=self.device)
         self._grad = torch.zeros_like(self._flat)
         self._loss = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._staging = None
@@ -173,6 +180,10 @@ class Trainer:
         return model, flat
 
     def _refresh_prepared(self) -> None:
+        if self._wide:
+            from . import wide
+            wide.prepare_wide(self.model.state_dict(), self.device, out=self._prepared)  # parameters are views of _flat
+            return
         from . import ops
         ops.prepare_from_flat(self._flat, self._nl, self._H, self._C, out=self._prepared)
 
@@ -180,8 +191,9 @@ class Trainer:
         """A frozen copy of the online network (get_train_agent / get_val_agent, trainer.py:123-134)."""
         model, flat = self._construct_flat_model(self._flat.clone())
         model.eval()
-        model._prepared = self._prepared.clone()
-        model._prepared_key = (str(self.device),) + tuple((p.data_ptr(), p._version) for p in model.parameters())
+        if not self._wide:  # wide models are prepared by the agent's WideRunner
+            model._prepared = self._prepared.clone()
+            model._prepared_key = (str(self.device),) + tuple((p.data_ptr(), p._version) for p in model.parameters())
         return model
 
     # -- checkpoints (trainer.py:73-121) ---------------------------------------------------------------
@@ -219,8 +231,13 @@ class Trainer:
             trainer.total_steps = state["total_steps"]
             trainer.total_battles = state["total_battles"]
             trainer.target_model.load_state_dict(state["target_model"])
-            from . import ops
-            ops.prepare_from_flat(trainer._flat_target, trainer._nl, trainer._H, trainer._C, out=trainer._prepared_target)
+            if trainer._wide:
+                from . import wide
+                wide.prepare_wide(trainer.target_model.state_dict(), trainer.device, out=trainer._prepared_target)
+            else:
+                from . import ops
+                ops.prepare_from_flat(trainer._flat_target, trainer._nl, trainer._H, trainer._C,
+                                      out=trainer._prepared_target)
             trainer.optimizer.load_state_dict(state["optimizer"])
             trainer.replay_buffer = state["replay_buffer"]
             trainer.update_loss_history = state["update_loss_history"]
@@ -286,6 +303,8 @@ class Trainer:
         (sum of this shard's Huber terms / n_global; the all-reduced mean when distributed)."""
         n = len(state)
         n_global = n if n_global is None else n_global
+        if self._wide:
+            return self._update_wide(state, next_state, action, reward, terminal, n_global)
         self._ensure_staging(max(n, 1))
         S = self._staging
         S["h_state"][:n * PK_OBS_BYTES] = np.ascontiguousarray(state).view(np.uint8).reshape(-1)
@@ -319,6 +338,47 @@ class Trainer:
         N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
                                   opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
                                   opt.betas[1], opt.eps, opt.step_count, self._prepared.data_ptr(), stream))
+        return float(self._loss.item())
+
+    def _update_wide(self, state, next_state, action, reward, terminal, n_global: int) -> float:
+        """The same Double-DQN step for a wide network (tensor-core path): Q(s, a) of the CHOSEN column with the
+        activations kept (trainer.py:163), online + target forward over next_state (:171-177), Huber dq (:184-187),
+        backward to the flat gradient (:192), [allreduce], clamp + Adam (:193-195), bf16 weights re-derived."""
+        from . import ops, wide
+        n = len(state)
+        dev, A = self.device, self.feature_extractor.output_dim
+        lib = N.lib()
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        if n == 0:
+            self._grad.zero_()
+            self._loss.zero_()
+        else:
+            ws = getattr(self, "_wide_ws", None)
+            if ws is None or self._wide_ws_n < n:
+                self._wide_ws = ws = wide.train_workspace(self._nl, self._H, n, A, dev)
+                self._wide_fw = wide.workspace(self._nl, self._H, n, A, dev)
+                self._wide_ws_n = n
+            s_d, s2_d = ops.packed_to_device(state, dev), ops.packed_to_device(next_state, dev)
+            a_d = torch.from_numpy(np.ascontiguousarray(action, dtype=np.int32)).to(dev)
+            r_d = torch.from_numpy(np.ascontiguousarray(reward, dtype=np.float32)).to(dev)
+            t_d = torch.from_numpy(np.ascontiguousarray(terminal, dtype=np.uint8)).to(dev)
+            m2, q_no, _ = wide.wide_forward(s2_d, A, self._prepared, self._nl, self._H, ws=self._wide_fw)
+            _, q_nt, _ = wide.wide_forward(s2_d, A, self._prepared_target, self._nl, self._H, ws=self._wide_fw)
+            _, q_sa = wide.train_forward(s_d, A, self._prepared, self._nl, self._H, ws, col_select=a_d)
+            dq, loss = wide.dqn_dq(q_sa, q_no if self.double_dqn else None, q_nt, m2, r_d, t_d, n_global, self.gamma,
+                                   self.double_dqn)
+            wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True)
+            self._loss.copy_(loss)
+        dist = self._dist()
+        if dist is not None:
+            from .dist import allreduce_sum_
+            allreduce_sum_(self._grad, self._loss, dist)
+        opt = self.optimizer
+        opt.step_count += 1
+        N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
+                                  opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
+                                  opt.betas[1], opt.eps, opt.step_count, None, stream))
+        self._refresh_prepared()
         return float(self._loss.item())
 
     def _update(self):

@@ -42,7 +42,7 @@ def gemm_bf16(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = N
     return out
 
 
-def prepare_wide(state_dict: dict, device) -> tuple:
+def prepare_wide(state_dict: dict, device, out: Optional[torch.Tensor] = None) -> tuple:
     """state_dict (reference key names) -> (prepared uint8 buffer on device, n_layers, n_channels)."""
     dev = torch.device(device)
     N.ensure_init(dev.index if dev.index is not None else torch.cuda.current_device())
@@ -67,7 +67,8 @@ def prepare_wide(state_dict: dict, device) -> tuple:
     bo = state_dict["output.bias"].detach().to(dev, torch.float32).contiguous()
     keep += [wo, bo]
     m.w_out, m.b_out = wo.data_ptr(), bo.data_ptr()
-    prepared = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    prepared = out if out is not None else torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    assert prepared.numel() == nbytes and prepared.dtype == torch.uint8
     N.check(lib.pk_wide_prepare(C.byref(m), prepared.data_ptr(), _stream_ptr(dev)))
     torch.cuda.current_stream(dev).synchronize()  # the fp32 staging copies in `keep` may be freed now
     return prepared, nl, H
@@ -164,24 +165,46 @@ def train_workspace(n_layers: int, H: int, B: int, A: int, device) -> torch.Tens
 
 
 def train_forward(packed: torch.Tensor, A: int, prepared: torch.Tensor, n_layers: int, H: int, ws: torch.Tensor,
-                  out_q: Optional[torch.Tensor] = None, out_mask: Optional[torch.Tensor] = None):
-    """Forward that keeps the activations in `ws` for train_backward.  Returns (mask (B, A), q (B, A))."""
+                  out_q: Optional[torch.Tensor] = None, out_mask: Optional[torch.Tensor] = None,
+                  col_select: Optional[torch.Tensor] = None):
+    """Forward that keeps the activations in `ws` for train_backward.  Returns (mask (B, A), q).
+    col_select None: q is (B, A), every column is a GEMM row.  col_select (B,) int32: q is (B,), only that column of
+    each battle is evaluated (the gather of trainer.py:163)."""
     dev = _dev(packed)
     B = _check_packed(packed)
     mask = out_mask if out_mask is not None else torch.empty((B, A), dtype=torch.int32, device=dev)
-    q = out_q if out_q is not None else torch.empty((B, A), dtype=torch.float32, device=dev)
-    N.check(N.lib().pk_wide_train_forward(packed.data_ptr(), B, A, prepared.data_ptr(), n_layers, H, ws.data_ptr(),
-                                          mask.data_ptr(), q.data_ptr(), _stream_ptr(dev)))
+    if col_select is not None:
+        assert col_select.dtype == torch.int32 and col_select.numel() == B and col_select.is_cuda
+    q = out_q if out_q is not None else torch.empty((B,) if col_select is not None else (B, A), dtype=torch.float32,
+                                                    device=dev)
+    N.check(N.lib().pk_wide_train_forward(packed.data_ptr(), B, A,
+                                          col_select.data_ptr() if col_select is not None else None,
+                                          prepared.data_ptr(), n_layers, H, ws.data_ptr(), mask.data_ptr(), q.data_ptr(),
+                                          _stream_ptr(dev)))
     return mask, q
 
 
 def train_backward(prepared: torch.Tensor, n_layers: int, H: int, B: int, A: int, ws: torch.Tensor, dq: torch.Tensor,
-                   out_grad: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """dq (B, A) fp32 = d loss / d q -> flat fp32 gradient in state_dict order."""
+                   out_grad: Optional[torch.Tensor] = None, chosen_only: bool = False) -> torch.Tensor:
+    """dq = d loss / d q ((B, A), or (B,) after a col_select forward) -> flat fp32 gradient in state_dict order."""
     dev = _dev(dq)
-    assert dq.dtype == torch.float32 and dq.is_contiguous() and dq.numel() == B * A
+    assert dq.dtype == torch.float32 and dq.is_contiguous() and dq.numel() == (B if chosen_only else B * A)
     n = N.lib().pk_mlp_param_floats(n_layers, H, n_channels())
     grad = out_grad if out_grad is not None else torch.empty(n, dtype=torch.float32, device=dev)
-    N.check(N.lib().pk_wide_train_backward(prepared.data_ptr(), n_layers, H, B, A, ws.data_ptr(), dq.data_ptr(),
-                                           grad.data_ptr(), _stream_ptr(dev)))
+    N.check(N.lib().pk_wide_train_backward(prepared.data_ptr(), n_layers, H, B, A, 1 if chosen_only else 0,
+                                           ws.data_ptr(), dq.data_ptr(), grad.data_ptr(), _stream_ptr(dev)))
     return grad
+
+
+def dqn_dq(q_sa, q_next_online, q_next_target, mask_next, reward, terminal, n_global: int, gamma: float,
+           double_dqn: bool = True):
+    """Double-DQN target + Huber loss + dq for the chosen columns (trainer.py:163-187).  Returns (dq (n,), loss (1,))."""
+    dev = _dev(q_sa)
+    n, A = q_next_target.shape
+    dq = torch.empty(n, dtype=torch.float32, device=dev)
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    N.check(N.lib().pk_wide_dqn_dq(q_sa.data_ptr(), q_next_online.data_ptr() if q_next_online is not None else None,
+                                   q_next_target.data_ptr(), mask_next.data_ptr(), reward.data_ptr(), terminal.data_ptr(),
+                                   n, A, int(n_global), float(gamma), 1 if double_dqn else 0, dq.data_ptr(),
+                                   loss.data_ptr(), _stream_ptr(dev)))
+    return dq, loss
