@@ -141,12 +141,20 @@ def main():
                          torch.from_numpy(hs[4]).to(dev)))
     Cn = ops.n_channels()
     from pokeai_b200 import _native as N
-    scratch = torch.empty(N.lib().pk_dqn_scratch_floats(nl, H, Cn, max(n, 1)), dtype=torch.float32, device=dev)
+    wide_net = tr._wide
+    scratch = None if wide_net else torch.empty(N.lib().pk_dqn_scratch_floats(nl, H, Cn, max(n, 1)),
+                                                dtype=torch.float32, device=dev)
     opt = tr.optimizer
     step_no = [0]
 
     def step(i):
         s, s2, a, r, t = dev_sets[i % n_rot]
+        if wide_net:  # tensor-core path: 2 next-state forwards, chosen-column forward + backward, clamp + Adam
+            loss = tr._wide_grad_device(s, s2, a, r, t, NG)
+            if world > 1:
+                dist.all_reduce(tr._grad, op=dist.ReduceOp.SUM)
+            tr._wide_apply()
+            return loss
         grad, loss = ops.dqn_grad(tr._prepared, tr._prepared_target, nl, H, A, s, s2, a, r, t, tr.gamma, True,
                                   n_global=NG, scratch=scratch)
         if world > 1:
@@ -202,10 +210,13 @@ def main():
         # forward + backward of the chosen action (weight gradients of the 64x64 layer dominate)
         hid = (nl - 1) * H * H
         fma_per = 2 * (50 * H + 9 * (8 * H + hid + H)) + (58 * H + hid + H) + (2 * hid + 58 * H + 2 * H)
+        if wide_net:  # dense GEMMs: 2 x 9-column forwards + 1-column forward, dW of every layer, dX of all but layer 0
+            fwd = H * (617 + (nl - 1) * H + 1)
+            fma_per = 2 * 9 * fwd + fwd + fwd + (nl - 1) * H * H
         line = {
             "metric": METRIC, "value": NG * args.steps / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": ("bf16 (fp32 accumulate)" if wide_net else "f32"), "data": "synthetic",
             "config": {"workload": f"DQN minibatch update, {NG} packed transitions per step (BASELINE configs[3]), "
                                    f"default MLP {nl}x{H}, Double DQN, gamma 0.95, 5% terminal",
                        "global_transitions_per_step": NG, "transitions_per_gpu": n,
@@ -213,16 +224,24 @@ def main():
                                    f"{tr._flat.numel()} fp32 gradients per step, clamp + Adam after the reduce",
                        "l2": f"{n_rot} rotating transition sets; inputs are 297 B per transition (9.7 MB per set), "
                              "the kernels are compute/latency-bound, not HBM-bound"},
-            "roofline": {"bound": "fp32-fma (packed replay moved the update off the HBM roofline)",
+            "roofline": {"bound": "tensor (bf16 tcgen05 GEMMs)" if wide_net else
+                         "fp32-fma (packed replay moved the update off the HBM roofline)",
                          "achieved": alg_bytes / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg_bytes / (ms * 1e-3) / 1e9 / peak, "traffic": None,
                          "algorithmic_bytes_per_step": alg_bytes, "peak_source": peak_src,
                          "fma_per_transition": fma_per,
-                         "achieved_tflops_fp32": 2 * fma_per * n / (ms * 1e-3) / 1e12,
+                         "achieved_tflops": 2 * fma_per * n / (ms * 1e-3) / 1e12,
                          "peak_tflops_fp32_nominal": 148 * 128 * 2 * 1.965e9 / 1e12},
-            "e2e": e2e, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches_per_step": 7,
+            "e2e": e2e, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches_per_step": (3 * (nl + 3) + 5 * nl + 8) if wide_net else 7,
             "last_loss": last_loss,
         }
+        if wide_net:  # tensor roofline: useful FLOPs / time against the measured sustained bf16 rate
+            import bench_wide
+            tpeak, tsrc = bench_wide.tensor_peak()
+            ach = 2 * fma_per * n / (ms * 1e-3) / 1e12
+            line["roofline"] = {"bound": "tensor", "achieved": ach, "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
+                                "traffic": None, "kernel": "pk_wide_gemm_kernel", "flops_per_transition": 2 * fma_per,
+                                "peak_source": tsrc}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -340,6 +340,33 @@ class Trainer:
                                   opt.betas[1], opt.eps, opt.step_count, self._prepared.data_ptr(), stream))
         return float(self._loss.item())
 
+    def _wide_grad_device(self, s_d, s2_d, a_d, r_d, t_d, n_global: int):
+        """Device-resident part of the wide update: fills self._grad, returns the loss tensor (1,)."""
+        from . import wide
+        n, A = s_d.shape[0], self.feature_extractor.output_dim
+        if getattr(self, "_wide_ws", None) is None or self._wide_ws_n < n:
+            self._wide_ws = wide.train_workspace(self._nl, self._H, n, A, self.device)
+            self._wide_fw = wide.workspace(self._nl, self._H, n, A, self.device)
+            self._wide_ws_n = n
+        ws = self._wide_ws
+        m2, q_no, _ = wide.wide_forward(s2_d, A, self._prepared, self._nl, self._H, ws=self._wide_fw)
+        _, q_nt, _ = wide.wide_forward(s2_d, A, self._prepared_target, self._nl, self._H, ws=self._wide_fw)
+        _, q_sa = wide.train_forward(s_d, A, self._prepared, self._nl, self._H, ws, col_select=a_d)
+        dq, loss = wide.dqn_dq(q_sa, q_no if self.double_dqn else None, q_nt, m2, r_d, t_d, n_global, self.gamma,
+                               self.double_dqn)
+        wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True)
+        return loss
+
+    def _wide_apply(self) -> None:
+        """clamp + Adam on the flat parameters, then the bf16 / transposed weight copies are re-derived"""
+        opt = self.optimizer
+        opt.step_count += 1
+        N.check(N.lib().pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
+                                      opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
+                                      opt.betas[1], opt.eps, opt.step_count, None,
+                                      torch.cuda.current_stream(self.device).cuda_stream))
+        self._refresh_prepared()
+
     def _update_wide(self, state, next_state, action, reward, terminal, n_global: int) -> float:
         """The same Double-DQN step for a wide network (tensor-core path): Q(s, a) of the CHOSEN column with the
         activations kept (trainer.py:163), online + target forward over next_state (:171-177), Huber dq (:184-187),
@@ -353,32 +380,17 @@ class Trainer:
             self._grad.zero_()
             self._loss.zero_()
         else:
-            ws = getattr(self, "_wide_ws", None)
-            if ws is None or self._wide_ws_n < n:
-                self._wide_ws = ws = wide.train_workspace(self._nl, self._H, n, A, dev)
-                self._wide_fw = wide.workspace(self._nl, self._H, n, A, dev)
-                self._wide_ws_n = n
             s_d, s2_d = ops.packed_to_device(state, dev), ops.packed_to_device(next_state, dev)
             a_d = torch.from_numpy(np.ascontiguousarray(action, dtype=np.int32)).to(dev)
             r_d = torch.from_numpy(np.ascontiguousarray(reward, dtype=np.float32)).to(dev)
             t_d = torch.from_numpy(np.ascontiguousarray(terminal, dtype=np.uint8)).to(dev)
-            m2, q_no, _ = wide.wide_forward(s2_d, A, self._prepared, self._nl, self._H, ws=self._wide_fw)
-            _, q_nt, _ = wide.wide_forward(s2_d, A, self._prepared_target, self._nl, self._H, ws=self._wide_fw)
-            _, q_sa = wide.train_forward(s_d, A, self._prepared, self._nl, self._H, ws, col_select=a_d)
-            dq, loss = wide.dqn_dq(q_sa, q_no if self.double_dqn else None, q_nt, m2, r_d, t_d, n_global, self.gamma,
-                                   self.double_dqn)
-            wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True)
+            loss = self._wide_grad_device(s_d, s2_d, a_d, r_d, t_d, n_global)
             self._loss.copy_(loss)
         dist = self._dist()
         if dist is not None:
             from .dist import allreduce_sum_
             allreduce_sum_(self._grad, self._loss, dist)
-        opt = self.optimizer
-        opt.step_count += 1
-        N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
-                                  opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
-                                  opt.betas[1], opt.eps, opt.step_count, None, stream))
-        self._refresh_prepared()
+        self._wide_apply()
         return float(self._loss.item())
 
     def _update(self):
