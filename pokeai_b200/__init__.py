@@ -11,6 +11,7 @@ _LAZY = {
     "FeatureExtractor": ".feature_extractor", "MLPModel": ".mlp_model", "Agent": ".agent", "AgentVal": ".agent",
     "AgentTrain": ".agent", "ReplayBuffer": ".replay_buffer", "ReplayBufferItem": ".replay_buffer",
     "Trainer": ".trainer", "DQN_DEFAULT_PARAMS": ".trainer", "DecisionSession": ".session",
+    "PartyEvaluator": ".party_evaluator", "PartyEvaluatorQuick": ".party_evaluator",
 }
 
 
