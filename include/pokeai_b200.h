@@ -141,6 +141,13 @@ PK_API int pk_n_channels(void);
 /* Debugging aid: when non-NULL, pk_encode / pk_decide record %globaltimer (ns) of lane 0 at 10 phase points of
  * the first battle of every warp into device_buffer[(cta * warps + warp) * 16 + phase].  NULL switches it off. */
 PK_API int pk_debug_set_trace(unsigned long long* device_buffer);
+/* pk_decide / pk_encode launches carry the programmatic-dependent-launch attribute (default on; PK_PDL=0 or
+ * pk_set_overlap_launches(0) turns it off): the part of the kernel that only reads the PACKED RECORDS and fills shared
+ * memory may overlap the tail of the previous kernel of the stream; weights are read and all outputs are written after
+ * griddepcontrol.wait, i.e. after that kernel has completed.  Contract: the packed records must not be produced by the
+ * kernel launched immediately before on the same stream (records that arrive by cudaMemcpy, or that were written
+ * earlier, are fine -- every caller in this repository satisfies this).  Worth 2 us per 4 096-state launch. */
+PK_API int pk_set_overlap_launches(int on);
 /* Tuning / test aid: which pk_decide kernel runs for networks of <= 64 channels.  0 = one battle per warp,
  * 2 = two battles per warp (one per half-warp in the MLP), 1 (default) = paired only when features are not
  * materialised (the measured optimum, profiles/r01_pair_vs_single.txt).  Results are identical up to fp32

@@ -55,6 +55,7 @@ _SIGNATURES = {
     "pk_last_error": (C.c_char_p, []),
     "pk_init": (C.c_int, [C.POINTER(pk_tables), _i]),
     "pk_debug_set_trace": (C.c_int, [_vp]),
+    "pk_set_overlap_launches": (C.c_int, [_i]),
     "pk_debug_set_pairing": (C.c_int, [_i]),
     "pk_debug_set_hidden_tc": (C.c_int, [_i]),
     "pk_n_channels": (C.c_int, []),

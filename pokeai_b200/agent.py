@@ -38,7 +38,22 @@ class Agent:
     def _session(self, n: int):
         s = self._feature_extractor.session(n)
         m = self._model
-        s.use_prepared(m.prepared(s.device), m.n_layers, m.n_channels) if hasattr(m, "prepared") else s.load_model(m)
+        # cheap change detector (the full key lives in MLPModel.prepared): parameter versions and storage pointers
+        plist = self.__dict__.get("_plist")
+        if plist is None:
+            plist = self._plist = list(m.parameters()) + list(m.buffers())
+        fast = (id(s),) + tuple(p._version for p in plist) + tuple(p.data_ptr() for p in plist)
+        if self.__dict__.get("_fast_key") == fast and getattr(s, "_prepared_ref", None) is self.__dict__.get("_last_prep"):
+            return s  # same parameters, and no other agent has re-pointed the shared session since
+        if hasattr(m, "prepared"):
+            prep = m.prepared(s.device)  # rebuilt (a NEW tensor) only when a parameter changed
+            if getattr(s, "_prepared_ref", None) is not prep:  # (re)pointing synchronises: do it only on a change
+                s.use_prepared(prep, m.n_layers, m.n_channels)
+            self._last_prep = prep
+        else:
+            s.load_model(m)
+            self._last_prep = None
+        self._fast_key = fast
         return s
 
     # -- dense-input Q (agent.py:23-30; used by party_evaluator.py:102, party_evaluator_quick.py:101) ---
@@ -71,8 +86,12 @@ class Agent:
         action (B,) int32).  Views of pinned buffers, valid until the next call."""
         n = len(obs_list)
         m = self._model
-        from .wide import WideRunner, is_wide
-        if hasattr(m, "n_channels") and is_wide(m.n_channels):
+        wide_net = self.__dict__.get("_is_wide")
+        if wide_net is None:
+            from .wide import is_wide
+            wide_net = self._is_wide = bool(hasattr(m, "n_channels") and is_wide(m.n_channels))
+        if wide_net:
+            from .wide import WideRunner
             # wide network (e.g. 4 x 2048): tensor-core path (pokeai_b200/wide.py), same semantics
             from .ops import SelectSpec
             fe = self._feature_extractor

@@ -212,3 +212,6 @@ __device__ __forceinline__ void pk_mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void pk_fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 __device__ __forceinline__ float pk_ldg_f(const float* p) { return __ldg(p); }
+// programmatic dependent launch (cudaLaunchAttributeProgrammaticStreamSerialization)
+__device__ __forceinline__ void pk_grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pk_grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

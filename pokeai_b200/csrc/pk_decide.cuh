@@ -552,6 +552,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   const int HS = tc ? PK_TC_HS : HP;                                // row stride of hbuf
   const PkSmemPlan plan = pk_smem_plan(lay, AT, nwarps, with_mlp, use_tma, tc);
 
+  pk_grid_launch_dependents();  // the next launch of the stream may begin its own read-only prologue
   unsigned long long* tr = sel.trace;
   const int tslot = blockIdx.x * nwarps + warp;
   pk_trace(tr, tslot, 0);
@@ -574,24 +575,12 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   uint4 cur = make_uint4(0u, 0u, 0u, 0u);
   if (b < B && lane < 9) cur = __ldg(packed + b * 9 + lane);
 
-  // the network's small tensors (biases, hidden matrices, head; the 50 state rows of W0^T: 30 KB for 2 x 64) are
-  // staged by two TMA bulk loads issued by one thread; everybody else goes on to the zero tile and the first
-  // record, and waits on the mbarrier only after the prologue barrier
   uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + plan.mbar);
   if (with_mlp && threadIdx.x == 0) {
-    const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
     pk_mbar_init(wbar, 1);
     pk_fence_mbar_init();
-    pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
-    pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
-    pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
   }
   const uint4* wfrag = reinterpret_cast<const uint4*>(smem + plan.wfrag);
-  if constexpr (TC) {
-    if (with_mlp)
-      for (int l = 1; l < lay.n_layers; ++l)
-        pk_tc_build_wfrag(prep + lay.wl[l], reinterpret_cast<uint4*>(smem + plan.wfrag) + (l - 1) * 2048);
-  }
   const float* zero_tile = nullptr;
   if (use_tma) {
     float4* z = reinterpret_cast<float4*>(smem + plan.zero_tile);
@@ -606,7 +595,6 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
     if (b + stride < B && lane < 9) cur = __ldg(packed + (b + stride) * 9 + lane);  // prefetch, consumed next turn
     __syncwarp();
     const int na = min((int)r[PK_OFF_NACT], A);
-    if (mask != nullptr && lane < A) mask[b * A + lane] = lane < na ? 1 : 0;  // feature_extractor.py:50-51
     sv[lane] = pk_state_feature(r, lane);
     sv[lane + 32] = pk_state_feature(r, lane + 32);
 #pragma unroll
@@ -624,10 +612,29 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   if (b < B) take_and_parse();
   pk_trace(tr, tslot, 2);
   if (with_mlp || use_tma) __syncthreads();
-  if (with_mlp) pk_mbar_wait(wbar, 0);  // the staged weights have landed (async proxy -> visible after the wait)
+  // Programmatic dependent launch: everything above reads only the packed records and fills shared memory, so it
+  // may run while the previous launch of this stream is still finishing.  Weights (which a preceding pk_clamp_adam may
+  // have written) are read and every global WRITE happens below this wait, which returns once the preceding kernel
+  // has completed and flushed.  Both griddepcontrol instructions are no-ops for a normal launch.
+  pk_grid_dependency_wait();
+  // the network's small tensors (biases, hidden matrices, head; the 50 state rows of W0^T: 30 KB for 2 x 64) are
+  // staged by two TMA bulk loads issued by one thread; they land while the first battle's features are stored, and
+  // the mbarrier is waited for just before the first use of the weights
+  if (with_mlp && threadIdx.x == 0) {
+    const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
+    pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
+    pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
+    pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
+  }
+  if constexpr (TC) {
+    if (with_mlp) {
+      for (int l = 1; l < lay.n_layers; ++l)
+        pk_tc_build_wfrag(prep + lay.wl[l], reinterpret_cast<uint4*>(smem + plan.wfrag) + (l - 1) * 2048);
+      __syncthreads();
+    }
+  }
   pk_trace(tr, tslot, 3);
   float b1r[CPL];
-  if (with_mlp) pk_lds_vec<CPL>(s_tail, lane, b1r);  // lay.b[0] is the start of the tail
 
   for (bool first = true; b < B; b += stride, first = false) {
     if (!first) {
@@ -635,6 +642,7 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
       take_and_parse();
     }
     const int n_act = min((int)r[PK_OFF_NACT], A);
+    if (mask != nullptr && lane < A) mask[b * A + lane] = lane < n_act ? 1 : 0;  // feature_extractor.py:50-51
 
     float* gfeat = feat != nullptr ? feat + (size_t)b * L : nullptr;
     if (gfeat != nullptr) {
@@ -654,6 +662,10 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
       continue;
     }
 
+    if (first) {
+      pk_mbar_wait(wbar, 0);  // the staged weights have landed (async proxy -> visible after the wait)
+      pk_lds_vec<CPL>(s_tail, lane, b1r);  // lay.b[0] is the start of the tail
+    }
     constexpr int GD = CPL <= 2 ? (AT < 4 ? AT : 4) : (AT < 2 ? AT : 2);  // gather ring depth (columns in flight)
     float gr[GD][8][CPL];
 #pragma unroll

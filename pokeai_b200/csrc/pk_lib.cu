@@ -46,6 +46,8 @@ struct PkGlobal {
   int encode_warps = 16;
   int decide_pair = 1;
   int hidden_tc = 0;
+  int pdl = 1;        // pk_decide launches carry the programmatic-stream-serialization attribute (PK_PDL)
+  int zero_copy = 1;  // host-buffer calls: kernels read / write pinned host buffers directly (PK_ZERO_COPY)
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
@@ -92,6 +94,8 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
   g.hidden_tc = env_int("PK_HIDDEN_TC", 0, 0, 1);  // 64-channel hidden layers on the 3xTF32 mma.sync path (measured: no gain)
+  g.pdl = env_int("PK_PDL", 1, 0, 1);
+  g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   return PK_OK;
 }
@@ -103,6 +107,10 @@ extern "C" int pk_init(const pk_tables* t, int device) {
 
 extern "C" int pk_debug_set_trace(unsigned long long* device_buffer) {
   g.trace = device_buffer;
+  return PK_OK;
+}
+extern "C" int pk_set_overlap_launches(int on) {
+  g.pdl = on ? 1 : 0;
   return PK_OK;
 }
 extern "C" int pk_debug_set_hidden_tc(int on) {
@@ -163,6 +171,25 @@ template <typename K>
 static int pk_set_smem(K kernel, unsigned bytes) {
   PK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
   return PK_OK;
+}
+
+// Launch with (optionally) programmatic dependent launch: the kernel's read-only prologue may overlap the tail of the
+// previous kernel of the stream; it does griddepcontrol.wait before its first global write.
+template <typename... KArgs, typename... Args>
+static cudaError_t pk_launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, bool pdl,
+                                 Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 #define PK_DISPATCH_CPL_AT(CPL_, AT_, MACRO)                                 \
@@ -281,15 +308,15 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
       if (tc) {                                                                                               \
         int rc_ = pk_set_smem(pk_decide_kernel<2, A_, 512, true>, plan.total);                                \
         if (rc_) return rc_;                                                                                  \
-        pk_decide_kernel<2, A_, 512, true><<<grid, nwarps * 32, plan.total, st>>>(                            \
-            pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0);                                \
+        PK_CUDA(pk_launch_pdl(pk_decide_kernel<2, A_, 512, true>, grid, nwarps * 32, plan.total, st,          \
+                              g.pdl != 0, pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0)); \
         break;                                                                                                \
       }                                                                                                       \
     }                                                                                                         \
     int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                         \
     if (rc_) return rc_;                                                                                      \
-    pk_decide_kernel<C_, A_, 512><<<grid, nwarps * 32, plan.total, st>>>(pk, B, prepared, lay, feat, mask,    \
-                                                                         q, action, ps, use_tma ? 1 : 0);     \
+    PK_CUDA(pk_launch_pdl(pk_decide_kernel<C_, A_, 512>, grid, nwarps * 32, plan.total, st, g.pdl != 0, pk,   \
+                          B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0));                     \
   }
 #define PK_LAUNCH_DECIDE_A(C_)                                        \
   switch (A) {                                                        \
@@ -495,6 +522,18 @@ extern "C" int pk_session_use_prepared(pk_session* s, const float* prepared_dev,
   return PK_OK;
 }
 
+// Device-side alias of a pinned (page-locked, mapped) host buffer, or null for pageable memory.
+static void* pk_pinned_alias(const void* host) {
+  if (host == nullptr) return nullptr;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, host) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  if (at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) return nullptr;
+  return at.devicePointer;
+}
+
 extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
                                       float temperature, const float* u_explore_host, const float* u_pick_host,
                                       float* q_host, int32_t* action_host) {
@@ -503,7 +542,26 @@ extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, 
   PK_REQUIRE(s->prepared != nullptr, "pk_session_decide_host: no weights loaded");
   PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
   if (B == 0) return PK_OK;
-  PK_CUDA(cudaMemcpyAsync(s->d_packed, packed_host, (size_t)B * sizeof(pk_obs), cudaMemcpyHostToDevice, s->stream));
+  // Zero-copy: when the caller's buffers are pinned the kernel reads the records over PCIe itself (each is read once,
+  // one battle ahead of its use) and stores Q / actions straight into host memory: one launch and one synchronise
+  // instead of three copies around it.  Pageable buffers take the staged path.
+  const pk_obs* in_dev = s->d_packed;
+  float* q_dev = s->d_q;
+  int32_t* act_dev = s->d_action;
+  bool q_direct = false, act_direct = false;
+  if (g.zero_copy) {
+    if (void* p = pk_pinned_alias(packed_host)) in_dev = static_cast<const pk_obs*>(p);
+    if (void* p = pk_pinned_alias(q_host)) {
+      q_dev = static_cast<float*>(p);
+      q_direct = true;
+    }
+    if (void* p = pk_pinned_alias(action_host)) {
+      act_dev = static_cast<int32_t*>(p);
+      act_direct = true;
+    }
+  }
+  if (in_dev == s->d_packed)
+    PK_CUDA(cudaMemcpyAsync(s->d_packed, packed_host, (size_t)B * sizeof(pk_obs), cudaMemcpyHostToDevice, s->stream));
   pk_select_params sp;
   memset(&sp, 0, sizeof(sp));
   sp.mode = mode;
@@ -519,11 +577,12 @@ extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, 
     PK_CUDA(cudaMemcpyAsync(s->d_u_pick, u_pick_host, (size_t)B * sizeof(float), cudaMemcpyHostToDevice, s->stream));
     sp.u_pick = s->d_u_pick;
   }
-  int rc = pk_decide_impl(s->d_packed, B, s->A, s->prepared, s->n_layers, s->n_channels, s->d_feat, s->d_mask, s->d_q,
-                          s->d_action, &sp, s->stream);
+  int rc = pk_decide_impl(in_dev, B, s->A, s->prepared, s->n_layers, s->n_channels, s->d_feat, s->d_mask, q_dev, act_dev,
+                          &sp, s->stream);
   if (rc) return rc;
-  if (q_host) PK_CUDA(cudaMemcpyAsync(q_host, s->d_q, (size_t)B * s->A * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
-  if (action_host)
+  if (q_host && !q_direct)
+    PK_CUDA(cudaMemcpyAsync(q_host, s->d_q, (size_t)B * s->A * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+  if (action_host && !act_direct)
     PK_CUDA(cudaMemcpyAsync(action_host, s->d_action, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
   PK_CUDA(cudaStreamSynchronize(s->stream));
   return PK_OK;

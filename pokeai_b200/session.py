@@ -75,6 +75,7 @@ class DecisionSession:
         m.w_out = host(sd["output.weight"])
         m.b_out = host(sd["output.bias"])
         N.check(N.lib().pk_session_load_weights(self._h, C.byref(m)))
+        self._prepared_ref = None  # the session reads its own copy now
 
     def use_prepared(self, prepared: torch.Tensor, n_layers: int, n_channels: int) -> None:
         """Point the session at caller-owned prepared weights on the device (no copy)."""
