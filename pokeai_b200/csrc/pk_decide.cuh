@@ -845,59 +845,168 @@ __global__ void __launch_bounds__(256) pk_select_kernel(const float* __restrict_
 }
 
 // ---- dense-input forward: feat (B, C, A) -> q (B, A) ------------------------------------------------
-// For callers that hand in dense features (Agent._calc_q_vector[_batch], agent.py:23-30).  One warp
-// per battle: the (C, A) block is staged in shared memory with coalesced loads, rows that are entirely
-// zero are skipped (exact: 0 * w adds nothing), the rest accumulate rows of W1^T; then the same tail.
+// For callers that hand in dense features (Agent._calc_q_vector[_batch], agent.py:23-30).  HBM-bound by the
+// 4*C*A bytes it has to read per battle.  One warp per battle, 16 warps per CTA, persistent grid.
+//  * The (C, A) block is STREAMED, not staged: chunks of 32 rows (32*A floats, contiguous) go global -> shared
+//    memory with 4-byte cp.async (battle blocks are only 4-byte aligned: 4*C*A is not a multiple of 16) through a
+//    per-warp ring of PK_DENSE_DEPTH chunks that runs ahead across battle boundaries, so every warp always has
+//    DEPTH-1 chunks (3.4 KB at A = 9) in flight and no registers are spent on the copy.  In shared memory a row is
+//    padded to XS = 4, 8 or 12 floats, so a row is read with XS/4 16-byte loads (the kernel is bound by shared-memory
+//    instructions: 9 scalar loads per row were the largest share of them).
+//  * Rows that are entirely zero are skipped (exact: 0 * w adds nothing); one-hot features make ~80 % of the rows zero.
+//  * The rows of W0^T a non-zero feature row multiplies come from shared memory for rows < cache_rows (as many as fit
+//    beside the tail; the host sizes it) and from global memory, four loads in flight, above that.  With the carve-out
+//    at its maximum the L1 is tiny, and a serial chain of L2-latency row loads was what bound the first version.
+// Summation order: bias, then rows in ascending order -- the same as the first version (parity tests unchanged).
+#define PK_DENSE_DEPTH 4
+#define PK_DENSE_XS(AT) (((AT) + 3) & ~3)
+template <int XS>
+__device__ __forceinline__ void pk_dense_row(const float* row, float (&v)[XS]) {
+#pragma unroll
+  for (int i = 0; i < XS; i += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(row + i);
+    v[i] = t.x;
+    v[i + 1] = t.y;
+    v[i + 2] = t.z;
+    v[i + 3] = t.w;
+  }
+}
+__device__ __forceinline__ void pk_cp_async4(uint32_t sdst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void pk_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void pk_cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 template <int CPL, int AT>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(512, 1)
 pk_dense_forward_kernel(const float* __restrict__ feat, int B, int A, const float* __restrict__ prep, PkLayout lay,
-                        float* __restrict__ q) {
+                        int cache_rows, float* __restrict__ q) {
   constexpr int HP = 32 * CPL;
+  constexpr int D = PK_DENSE_DEPTH;
+  constexpr int XS = PK_DENSE_XS(AT);
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int L = lay.C * A;
-  // plan: tail | per warp { hbuf[AT*HP], xt[L rounded to 4] }
-  const unsigned tail_bytes = (lay.total - lay.b[0]) * 4u;
+  const int CH = 32 * A;                    // floats per chunk
+  const int nch = (lay.C + 31) >> 5;        // chunks per battle
+  // plan: tail | wcache[cache_rows][HP] | per warp { hbuf[AT*HP], ring[D][32][XS] }
+  const unsigned tail_floats = lay.total - lay.b[0];
+  float* s_tail = reinterpret_cast<float*>(smem);
+  float* s_wc = s_tail + tail_floats;
+  float* hbuf = s_wc + (size_t)cache_rows * HP + (size_t)warp * (AT * HP + D * 32 * XS);
+  float* ring = hbuf + AT * HP;
+  const float* w1t = prep + lay.w1t;
+
+  // padding words of the ring are never written by the copies: zero them once so the row scan reads zeros there
+  for (int i = lane; i < D * 32 * XS; i += 32) ring[i] = 0.0f;
+  int doff[AT];  // where element e = j*32 + lane of a chunk lands: row e / A, column e % A
+#pragma unroll
+  for (int j = 0; j < AT; ++j) {
+    const int e = j * 32 + lane;
+    doff[j] = ((e / A) * XS + (e % A)) * 4;  // byte offset inside a slot
+  }
+  const uint32_t ring_u32 = pk_smem_u32(ring);
+  __syncwarp();
+  // the ring starts before the weights are staged: records first, weights under their latency
+  const long long stride = (long long)gridDim.x * nwarps;
+  long long ib = (long long)blockIdx.x * nwarps + warp;  // battle / chunk / slot the next issue refers to
+  int ich = 0, islot = 0;
+  auto issue = [&]() {
+    if (ib < B) {
+      const int off = ich * CH;
+      const float* src = feat + (size_t)ib * L + off;
+      const int n = min(CH, L - off);
+      const uint32_t dst = ring_u32 + islot * (32 * XS * 4);
+#pragma unroll
+      for (int j = 0; j < AT; ++j) {
+        const int e = j * 32 + lane;
+        if (e < n) pk_cp_async4(dst + doff[j], src + e);
+      }
+    }
+    pk_cp_async_commit();
+    if (++ich == nch) {
+      ich = 0;
+      ib += stride;
+    }
+    islot = islot + 1 == D ? 0 : islot + 1;
+  };
+#pragma unroll
+  for (int i = 0; i < D - 1; ++i) issue();
+
   {
-    float4* dt = reinterpret_cast<float4*>(smem);
+    float4* dt = reinterpret_cast<float4*>(s_tail);
     const float4* st = reinterpret_cast<const float4*>(prep + lay.b[0]);
-    const int nt = (int)(tail_bytes >> 4);
+    const int nt = (int)(tail_floats >> 2);
     for (int i = threadIdx.x; i < nt; i += blockDim.x) dt[i] = __ldg(st + i);
+    float4* dw = reinterpret_cast<float4*>(s_wc);
+    const float4* sw = reinterpret_cast<const float4*>(w1t);
+    const int nw = cache_rows * (HP / 4);
+    for (int i = threadIdx.x; i < nw; i += blockDim.x) dw[i] = __ldg(sw + i);
   }
   __syncthreads();
-  const float* s_tail = reinterpret_cast<const float*>(smem);
-  const unsigned xt_floats = ((unsigned)L + 3u) & ~3u;
-  float* hbuf = reinterpret_cast<float*>(smem + tail_bytes) + (size_t)warp * (AT * HP + xt_floats);
-  float* xt = hbuf + AT * HP;
-  const float* w1t = prep + lay.w1t;
   float b1r[CPL];
   pk_lds_vec<CPL>(s_tail, lane, b1r);
 
-  for (long long b = (long long)blockIdx.x * nwarps + warp; b < B; b += (long long)gridDim.x * nwarps) {
-    const float* g = feat + (size_t)b * L;
-    __syncwarp();
-#pragma unroll 8
-    for (int i = lane; i < L; i += 32) xt[i] = __ldg(g + i);
-    __syncwarp();
+  int cslot = 0;
+  for (long long b = (long long)blockIdx.x * nwarps + warp; b < B; b += stride) {
     float h[AT][CPL];
 #pragma unroll
     for (int c = 0; c < AT; ++c)
 #pragma unroll
       for (int i = 0; i < CPL; ++i) h[c][i] = b1r[i];
-    for (int k0 = 0; k0 < lay.C; k0 += 32) {
-      const int k = k0 + lane;
+    for (int ch = 0; ch < nch; ++ch) {
+      __syncwarp();  // every lane is done with the slot the next issue overwrites
+      issue();
+      pk_cp_async_wait<D - 1>();
+      __syncwarp();
+      const float* xt = ring + cslot * (32 * XS);
+      cslot = cslot + 1 == D ? 0 : cslot + 1;
+      const int k0 = ch << 5;
       bool nz = false;
-      if (k < lay.C)
-        for (int c = 0; c < A; ++c) nz |= xt[k * A + c] != 0.0f;
+      if (k0 + lane < lay.C) {
+        float xv[XS];
+        pk_dense_row<XS>(xt + lane * XS, xv);
+#pragma unroll
+        for (int c = 0; c < AT; ++c)
+          if (c < A) nz |= xv[c] != 0.0f;
+      }
       unsigned rows = __ballot_sync(0xffffffffu, nz);
       while (rows) {
-        const int kk = k0 + __ffs(rows) - 1;
+        const int r0 = __ffs(rows) - 1;
         rows &= rows - 1u;
-        float w[CPL];
-        pk_ldg_vec<CPL>(w1t + (size_t)kk * HP, lane, w);
+        if (k0 + r0 < cache_rows) {
+          float w[CPL];
+          pk_lds_vec<CPL>(s_wc + (k0 + r0) * HP, lane, w);
+          float xv[XS];
+          pk_dense_row<XS>(xt + r0 * XS, xv);
 #pragma unroll
-        for (int c = 0; c < AT; ++c) {
-          if (c < A) pk_fma_vec<CPL>(h[c], w, xt[kk * A + c]);
+          for (int c = 0; c < AT; ++c)
+            if (c < A) pk_fma_vec<CPL>(h[c], w, xv[c]);
+        } else {  // rows ascend, so everything left in this chunk is uncached too: four row loads in flight
+          int r[4];
+          r[0] = r0;
+#pragma unroll
+          for (int t = 1; t < 4; ++t) {
+            r[t] = rows ? __ffs(rows) - 1 : -1;
+            rows &= rows - 1u;  // 0 & anything stays 0
+          }
+          float w[4][CPL];
+#pragma unroll
+          for (int t = 0; t < 4; ++t)
+            if (r[t] >= 0) pk_ldg_vec<CPL>(w1t + (size_t)(k0 + r[t]) * HP, lane, w[t]);
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            if (r[t] >= 0) {
+              float xv[XS];
+              pk_dense_row<XS>(xt + r[t] * XS, xv);
+#pragma unroll
+              for (int c = 0; c < AT; ++c)
+                if (c < A) pk_fma_vec<CPL>(h[c], w[t], xv[c]);
+            }
+          }
         }
       }
     }
@@ -913,6 +1022,7 @@ pk_dense_forward_kernel(const float* __restrict__ feat, int B, int A, const floa
       if (lane == c) myq = qv[c];
     if (lane < A) q[b * A + lane] = myq;
   }
+  pk_cp_async_wait<0>();
 }
 
 // ---- weight preparation: state_dict layout -> transposed / padded ---------------------------------------

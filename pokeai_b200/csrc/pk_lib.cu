@@ -47,6 +47,7 @@ struct PkGlobal {
   int decide_pair = 1;
   int hidden_tc = 0;
   int pdl = 1;        // pk_decide launches carry the programmatic-stream-serialization attribute (PK_PDL)
+  int dense_warps = 16;  // warps per CTA of the dense-input forward (PK_DENSE_WARPS; kernel iteration only)
   int zero_copy = 1;  // host-buffer calls: kernels read / write pinned host buffers directly (PK_ZERO_COPY)
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
@@ -96,6 +97,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.hidden_tc = env_int("PK_HIDDEN_TC", 0, 0, 1);  // 64-channel hidden layers on the 3xTF32 mma.sync path (measured: no gain)
   g.pdl = env_int("PK_PDL", 1, 0, 1);
   g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 1);
+  g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   return PK_OK;
 }
@@ -363,12 +365,15 @@ extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channel
   const PkLayout lay = pk_make_layout(n_layers, n_channels, in_channels);
   const int CPL = lay.HP / 32, AT = pk_at_for(A);
   const unsigned tail_bytes = (lay.total - lay.b[0]) * 4u;
-  const unsigned per_warp = ((unsigned)AT * lay.HP + (((unsigned)in_channels * A + 3u) & ~3u)) * 4u;
-  int nwarps = 8;
+  const unsigned per_warp = ((unsigned)AT * lay.HP + PK_DENSE_DEPTH * 32u * PK_DENSE_XS(AT)) * 4u;
+  int nwarps = g.dense_warps;
   while (nwarps > 1 && tail_bytes + per_warp * nwarps > (unsigned)g.max_smem) --nwarps;
-  const unsigned smem = tail_bytes + per_warp * nwarps;
-  if (smem > (unsigned)g.max_smem)
+  if (tail_bytes + per_warp * nwarps > (unsigned)g.max_smem)
     return pk_fail(PK_ERR_UNSUPPORTED, "network %d x %d does not fit the small-net forward kernel", n_layers, n_channels);
+  // the rest of shared memory caches the first rows of W0^T (all of them when they fit)
+  int cache_rows = (int)(((unsigned)g.max_smem - tail_bytes - per_warp * nwarps) / (lay.HP * 4u));
+  if (cache_rows > in_channels) cache_rows = in_channels;
+  const unsigned smem = tail_bytes + per_warp * nwarps + (unsigned)cache_rows * lay.HP * 4u;
   int grid = (B + nwarps - 1) / nwarps;
   if (grid > g.sm_count) grid = g.sm_count;
   cudaStream_t st = (cudaStream_t)stream;
@@ -376,7 +381,7 @@ extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channel
   {                                                                                              \
     int rc_ = pk_set_smem(pk_dense_forward_kernel<C_, A_>, smem);                                \
     if (rc_) return rc_;                                                                         \
-    pk_dense_forward_kernel<C_, A_><<<grid, nwarps * 32, smem, st>>>(feat, B, A, prepared, lay, q); \
+    pk_dense_forward_kernel<C_, A_><<<grid, nwarps * 32, smem, st>>>(feat, B, A, prepared, lay, cache_rows, q); \
   }
   PK_DISPATCH_CPL_AT(CPL, AT, PK_LAUNCH_DENSE);
 #undef PK_LAUNCH_DENSE
