@@ -131,7 +131,9 @@ class AgentVal(Agent):
     def act(self, obs: object, reward: float) -> int:
         q, a = self.q_and_action_batch([obs])
         action = int(a[0])
-        self._log_q(q[0], len(obs.possible_actions), action)
+        if logger.isEnabledFor(logging.DEBUG):
+            n_act = int(obs["n_act"][0]) if isinstance(obs, np.ndarray) else len(obs.possible_actions)
+            self._log_q(q[0], n_act, action)
         return action
 
     def stop_episode(self, reward: float) -> None:

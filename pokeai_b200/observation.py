@@ -39,6 +39,10 @@ class ActivePokeStatus:
         self.ranks: Dict[str, int] = {k: 0 for k in RANK_KEYS}
         self.volatile_statuses: Set[str] = set()
 
+    @property
+    def hp_ratio(self) -> float:  # battle_status.py:96
+        return self.hp_current / self.hp_max
+
 
 class SideStatus:
     def __init__(self):
@@ -47,6 +51,19 @@ class SideStatus:
         self.side_statuses: Set[str] = set()
         self.total_pokes = 0
         self.remaining_pokes = 0
+
+    # the two potentials RLPolicy's surrogate reward reads (battle_status.py:132-150)
+    def get_mean_hp_ratio(self) -> float:
+        assert self.total_pokes > 0
+        assert self.active is not None
+        # members that have not appeared yet count as full HP
+        ratio_sum = self.active.hp_ratio + sum(p.hp_ratio for p in self.reserve_pokes.values()) + (
+            self.total_pokes - 1 - len(self.reserve_pokes))
+        return ratio_sum / self.total_pokes
+
+    def get_alive_ratio(self) -> float:
+        assert self.total_pokes > 0
+        return self.remaining_pokes / self.total_pokes
 
 
 class BattleStatus:

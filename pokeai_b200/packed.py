@@ -59,9 +59,8 @@ def _status_code(s: str) -> int:
     return STATUS_CODE.get(s, STATUS_FNT)
 
 
-def pack_into(rec, obs, tables: Tables, max_actions: int = MAX_ACTIONS) -> None:
-    """Fill one record (a numpy void of PK_OBS_DTYPE) from an observation object."""
-    bs = obs.battle_status
+def pack_state_into(rec, bs, tables: Tables) -> None:
+    """The battle-state half of a record (offsets 0..30) from a BattleStatus-like object."""
     sides = (bs.side_friend, bs.side_opponent)
     for i, side in enumerate(sides):
         ss = bs.side_statuses[side]
@@ -79,6 +78,11 @@ def pack_into(rec, obs, tables: Tables, max_actions: int = MAX_ACTIONS) -> None:
     opp = bs.side_statuses[bs.side_opponent].active
     rec["opp_species"] = tables.species_name_to_idx[opp.species]  # KeyError like dex.get_pokedex_by_name
     rec["weather"] = WEATHER_CODE.get(bs.weather, 0)
+
+
+def pack_into(rec, obs, tables: Tables, max_actions: int = MAX_ACTIONS) -> None:
+    """Fill one record (a numpy void of PK_OBS_DTYPE) from an observation object."""
+    pack_state_into(rec, obs.battle_status, tables)
     acts = obs.possible_actions
     if len(acts) > max_actions:
         # feature_extractor.py:49 would raise a numpy broadcast ValueError here

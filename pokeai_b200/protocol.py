@@ -1,0 +1,177 @@
+"""Simulator request -> packed record, without PossibleAction strings in between.
+
+The reference turns every `|request|` JSON into a list of PossibleAction named tuples full of strings
+(get_possible_actions, pokeai/ai/common.py:143-174), wraps them in an RLPolicyObservation
+(rl_policy.py:95-98) and lets ChoiceToVec look every string up again (choice_to_vec.py:48-60).  Here the
+request is walked once and the integer indices go straight into the 144-byte record the kernels read
+(`pack_request`); the simulator keys ("move 2", "switch 5") are returned beside it so the chosen slot can be
+mapped back.  `PackedRLPolicy` is RLPolicy (rl_policy.py:16-125) on that path, and
+`PackedRLPolicy.choice_batch` is the lock-step form: one `act_batch` launch for every battle that is waiting
+for a decision.
+
+Same results as `pack_observation(RLPolicyObservation(bs, request, get_possible_actions(bs, request)))`
+(tests/test_protocol.py, against vectors produced by the reference's own get_possible_actions), same
+exceptions: KeyError on unknown names or a request without 'active', ValueError when the actions do not fit.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .packed import FLAG_FORCE, FLAG_SWITCH, PK_OBS_DTYPE, pack_state_into
+from .tables import MAX_ACTIONS, MAX_MOVES, Tables, load_tables
+
+
+def _active_move_id(move_id: str, name: str) -> str:
+    # common.py:17-21: "Hidden Power Dark 70" -> hiddenpowerdark
+    if move_id == "hiddenpower":
+        return "hiddenpower" + name.split(" ")[2].lower()
+    return move_id
+
+
+def _side_move_id(move_id: str) -> str:
+    # common.py:24-29: return102 -> return, frustration1 -> frustration
+    if move_id.startswith("return"):
+        return "return"
+    if move_id.startswith("frustration"):
+        return "frustration"
+    return move_id
+
+
+def pack_actions_into(rec, request: dict, tables: Tables, max_actions: int = MAX_ACTIONS) -> List[str]:
+    """Fill n_act / act[] of one record from a request; returns the simulator key of every slot.
+    Order and filtering are get_possible_actions' (common.py:143-174): party order; the active member gives one
+    slot per enabled move (none on a forced switch); a benched member gives a switch slot unless it has fainted
+    or the active one is trapped."""
+    force_switch = bool(request.get("forceSwitch"))
+    if not force_switch:
+        active = request["active"]
+        trapped = active[0].get("trapped")
+    else:
+        active = None
+        trapped = False
+    keys: List[str] = []
+    acts = rec["act"]
+    sp_idx, mv_idx, it_idx = tables.species_name_to_idx, tables.move_to_idx, tables.item_to_idx
+
+    def slot():
+        if len(keys) >= max_actions:
+            raise ValueError(f"more than {max_actions} possible actions")  # feature_extractor.py:49 broadcast error
+        return acts[len(keys)]
+
+    for poke_idx, member in enumerate(request["side"]["pokemon"]):
+        species = sp_idx[member["details"].split(",")[0]]  # "Kangaskhan, L50, F" (common.py:146-147)
+        if member["active"]:
+            if force_switch:
+                continue
+            item = it_idx[member["item"]]
+            for move_idx, move in enumerate(active[0]["moves"]):
+                if move.get("disabled"):
+                    continue
+                ar = slot()
+                ar["flags"] = 0
+                ar["species"] = species
+                ar["item"] = item
+                ar["n_moves"] = 1
+                ar["move"][0] = mv_idx[_active_move_id(move["id"], move["move"])]
+                keys.append(f"move {move_idx + 1}")
+        else:
+            if member["condition"].endswith(" fnt") or trapped:
+                continue
+            moves = member["moves"]
+            if len(moves) > MAX_MOVES:
+                raise ValueError("more than 4 moves on one action")
+            ar = slot()
+            ar["flags"] = FLAG_SWITCH | (FLAG_FORCE if force_switch else 0)
+            ar["species"] = species
+            ar["item"] = it_idx[member["item"]]
+            ar["n_moves"] = len(moves)
+            for j, m in enumerate(moves):
+                ar["move"][j] = mv_idx[_side_move_id(m)]
+            keys.append(f"switch {poke_idx + 1}")
+    rec["n_act"] = len(keys)
+    return keys
+
+
+def pack_request(battle_status, request: dict, tables: Optional[Tables] = None,
+                 max_actions: int = MAX_ACTIONS) -> Tuple[np.ndarray, List[str]]:
+    """(BattleStatus, request) -> ((1,) PK_OBS_DTYPE record, simulator keys)."""
+    rec, keys = pack_requests([(battle_status, request)], tables, max_actions)
+    return rec, keys[0]
+
+
+def pack_requests(pairs: Sequence[Tuple[object, dict]], tables: Optional[Tables] = None,
+                  max_actions: int = MAX_ACTIONS) -> Tuple[np.ndarray, List[List[str]]]:
+    tables = tables or load_tables()
+    out = np.zeros(len(pairs), dtype=PK_OBS_DTYPE)
+    keys = []
+    for i, (bs, request) in enumerate(pairs):
+        pack_state_into(out[i], bs, tables)
+        keys.append(pack_actions_into(out[i], request, tables, max_actions))
+    return out, keys
+
+
+class PackedRLPolicy:
+    """RLPolicy (rl_policy.py:16-125) with the request packed directly.  `agent` is an AgentVal / AgentTrain of
+    this package; `surrogate_reward_config` has hp_ratio / alive_ratio / only_opponent / offset_at_end
+    (surrogate_reward_config.py:4-15)."""
+
+    def __init__(self, agent, surrogate_reward_config, tables: Optional[Tables] = None):
+        self.agent = agent
+        self.surrogate_reward_config = surrogate_reward_config
+        self.last_reward_potential: Optional[float] = None
+        self.tables = tables or load_tables()
+        self._max_actions = agent._feature_extractor.output_dim
+
+    def game_start(self) -> None:
+        self.last_reward_potential = None
+
+    def _calc_reward_potential(self, battle_status) -> float:
+        c = self.surrogate_reward_config
+        sps = []
+        for side in (battle_status.side_friend, battle_status.side_opponent):  # rl_policy.py:66-70
+            ss = battle_status.side_statuses[side]
+            sps.append(ss.get_mean_hp_ratio() * c.hp_ratio + ss.get_alive_ratio() * c.alive_ratio)
+        return -sps[1] if c.only_opponent else sps[0] - sps[1]
+
+    def _surrogate(self, potential: float) -> float:
+        return potential - self.last_reward_potential if self.last_reward_potential is not None else 0.0
+
+    def _choice_by_model(self, battle_status, request: dict) -> str:
+        potential = self._calc_reward_potential(battle_status)
+        rec, keys = pack_request(battle_status, request, self.tables, self._max_actions)
+        if len(keys) == 1:  # rl_policy.py:88-92: a single choice never reaches the model
+            return keys[0]
+        action = self.agent.act(rec, self._surrogate(potential))
+        self.last_reward_potential = potential
+        return keys[action]
+
+    choice_turn_start = _choice_by_model
+    choice_force_switch = _choice_by_model
+
+    def game_end(self, reward: float) -> None:
+        if self.surrogate_reward_config.offset_at_end:
+            reward = reward - self.last_reward_potential
+        self.agent.stop_episode(reward)
+
+    @staticmethod
+    def choice_batch(policies: Sequence["PackedRLPolicy"], statuses: Sequence, requests: Sequence[dict]) -> List[str]:
+        """Greedy decisions of many battles that share ONE validation agent, in one launch.  Equivalent to calling
+        `choice_turn_start` / `choice_force_switch` on each policy in turn (an AgentVal ignores the reward, but the
+        potentials are kept so that `game_end` sees the same state)."""
+        if not policies:
+            return []
+        agent = policies[0].agent
+        if any(p.agent is not agent for p in policies):
+            raise ValueError("choice_batch needs policies that share one agent")
+        pots = [p._calc_reward_potential(bs) for p, bs in zip(policies, statuses)]
+        rec, keys = pack_requests(list(zip(statuses, requests)), policies[0].tables, policies[0]._max_actions)
+        multi = [i for i, k in enumerate(keys) if len(k) != 1]
+        out = [k[0] if len(k) == 1 else "" for k in keys]
+        if multi:
+            actions = agent.act_batch(rec[multi])
+            for i, a in zip(multi, actions):
+                out[i] = keys[i][int(a)]
+                policies[i].last_reward_potential = pots[i]
+        return out

@@ -1,0 +1,167 @@
+"""Request -> packed path against the reference's own get_possible_actions
+(tools/make_golden_protocol.py ran it in the build container; the GPU box has no reference)."""
+import copy
+import gzip
+import json
+from collections import namedtuple
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+
+@pytest.fixture(scope="module")
+def cases():
+    with gzip.open(GOLDEN / "protocol_requests.json.gz", "rt") as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="module")
+def statuses():
+    """real battle states from the recorded battle log, to sit beside the synthetic requests"""
+    from pokeai_b200.observation import battle_status_from_json
+    with gzip.open(GOLDEN / "fixture_decisions.json.gz", "rt") as f:
+        d = json.load(f)
+    return [battle_status_from_json(x["battle_status"]) for x in d]
+
+
+def test_pack_request_equals_possible_actions_route(cases, statuses, tables):
+    """bytes of pack_request == bytes of pack_observation(RLPolicyObservation(bs, request, reference's list)),
+    and the keys are the reference's simulator keys in order"""
+    from pokeai_b200.observation import RLPolicyObservation, possible_actions_from_json
+    from pokeai_b200.packed import pack_observation
+    from pokeai_b200.protocol import pack_request, pack_requests
+    n_checked = 0
+    for i, c in enumerate(cases):
+        bs = statuses[i % len(statuses)]
+        pas = possible_actions_from_json(c["possible_actions"])
+        rec, keys = pack_request(bs, c["request"], tables)
+        assert keys == [pa.simulator_key for pa in pas], i
+        want = pack_observation(RLPolicyObservation(bs, c["request"], pas), tables)
+        assert rec.tobytes() == want.tobytes(), i
+        n_checked += 1
+    assert n_checked == len(cases) >= 200
+    # batched form
+    pairs = [(statuses[i % len(statuses)], c["request"]) for i, c in enumerate(cases)]
+    recs, keys = pack_requests(pairs, tables)
+    assert recs.shape == (len(cases),) and all(int(r["n_act"]) == len(k) for r, k in zip(recs, keys))
+    assert recs[7].tobytes() == pack_request(*pairs[7], tables)[0].tobytes()
+
+
+def test_pack_request_errors(cases, statuses, tables):
+    from pokeai_b200.protocol import pack_request
+    bs = statuses[0]
+    turn = next(c["request"] for c in cases if c["request"].get("active") and len(c["request"]["side"]["pokemon"]) == 6)
+    r = copy.deepcopy(turn)
+    del r["active"]
+    with pytest.raises(KeyError):  # common.py:135 request['active']
+        pack_request(bs, r, tables)
+    r = copy.deepcopy(turn)
+    r["side"]["pokemon"][1]["details"] = "Missingno, L50"
+    with pytest.raises(KeyError):  # dex.get_pokedex_by_name
+        pack_request(bs, r, tables)
+    r = copy.deepcopy(turn)
+    r["side"]["pokemon"][0]["item"] = "notanitem"
+    with pytest.raises(KeyError):  # choice_to_vec.py item lookup
+        pack_request(bs, r, tables)
+    r = copy.deepcopy(turn)
+    for m in r["side"]["pokemon"]:
+        m["condition"] = "10/10"
+    r["active"][0].pop("trapped", None)
+    for m in r["active"][0]["moves"]:
+        m["disabled"] = False
+    n = len(r["active"][0]["moves"]) + 5
+    with pytest.raises(ValueError):  # more actions than the extractor's output_dim
+        pack_request(bs, r, tables, max_actions=n - 1)
+    assert len(pack_request(bs, r, tables, max_actions=n)[1]) == n
+
+
+Cfg = namedtuple("Cfg", "hp_ratio alive_ratio only_opponent offset_at_end")
+
+
+def _side(real, hp, alive):
+    """a real side status with the two ratio methods of the reference's SideStatus (battle_status.py:132-150)"""
+    ss = copy.copy(real)
+    ss.get_mean_hp_ratio = lambda: hp
+    ss.get_alive_ratio = lambda: alive
+    return ss
+
+
+class _FakeAgent:
+    """records what the policy hands to act / stop_episode"""
+
+    def __init__(self, output_dim):
+        fe = type("FE", (), {})()
+        fe.output_dim = output_dim
+        self._feature_extractor = fe
+        self.calls, self.stopped = [], []
+
+    def act(self, rec, reward):
+        self.calls.append((rec.copy(), reward))
+        return int(rec["n_act"][0]) - 1
+
+    def stop_episode(self, reward):
+        self.stopped.append(reward)
+
+
+def test_policy_rewards_and_single_choice(cases, statuses, tables):
+    """surrogate reward = potential difference, first decision 0.0, single choices bypass the model and leave the
+    potential untouched, offset_at_end subtracts the last potential (rl_policy.py:60-125)"""
+    from pokeai_b200.protocol import PackedRLPolicy
+    bs = copy.copy(statuses[0])
+    real = bs.side_statuses
+    bs.side_statuses = {bs.side_friend: _side(real[bs.side_friend], 0.8, 1.0),
+                        bs.side_opponent: _side(real[bs.side_opponent], 0.5, 2 / 3)}
+    multi = next(c["request"] for c in cases if len(c["possible_actions"]) >= 3)
+    single = next(c["request"] for c in cases if len(c["possible_actions"]) == 1)
+    agent = _FakeAgent(9)
+    pol = PackedRLPolicy(agent, Cfg(1.0, 0.5, False, True), tables)
+    pol.game_start()
+    k0 = pol.choice_turn_start(bs, multi)
+    p0 = (0.8 + 0.5) - (0.5 + 1 / 3)
+    assert agent.calls[-1][1] == 0.0 and pol.last_reward_potential == pytest.approx(p0)
+    assert k0 == [pa["simulator_key"] for pa in next(c for c in cases if c["request"] is multi)["possible_actions"]][-1]
+    bs.side_statuses[bs.side_opponent] = _side(real[bs.side_opponent], 0.25, 1 / 3)
+    assert pol.choice_force_switch(bs, single) in ("move 1", "move 2", "move 3", "move 4", "switch 1", "switch 2",
+                                                   "switch 3", "switch 4", "switch 5", "switch 6")
+    assert len(agent.calls) == 1 and pol.last_reward_potential == pytest.approx(p0)  # not consulted, not updated
+    pol.choice_turn_start(bs, multi)
+    p1 = (0.8 + 0.5) - (0.25 + 1 / 6)
+    assert agent.calls[-1][1] == pytest.approx(p1 - p0)
+    pol.game_end(1.0)
+    assert agent.stopped == [pytest.approx(1.0 - p1)]
+    pol2 = PackedRLPolicy(agent, Cfg(1.0, 0.0, True, False), tables)
+    pol2.game_start()
+    pol2.choice_turn_start(bs, multi)
+    assert pol2.last_reward_potential == pytest.approx(-0.25)
+
+
+@pytest.mark.gpu
+def test_policy_on_gpu_matches_object_route(cases, statuses, tables, dev):
+    """PackedRLPolicy (single calls and choice_batch) picks what AgentVal.act picks on the reference-style
+    observation objects"""
+    import torch
+    from pokeai_b200 import AgentVal, FeatureExtractor, MLPModel
+    from pokeai_b200.observation import RLPolicyObservation, possible_actions_from_json
+    from pokeai_b200.protocol import PackedRLPolicy
+    sel = [c for c in cases if c["party_size"] == 6][:64]
+    fe = FeatureExtractor(6)
+    torch.manual_seed(5)
+    model = MLPModel(fe.input_shape, fe.output_dim, n_layers=2, n_channels=64).to(dev)
+    agent = AgentVal(model, fe)
+    cfg = Cfg(0.0, 0.0, False, False)
+    want, pols, bss, reqs = [], [], [], []
+    for i, c in enumerate(sel):
+        bs = statuses[(3 * i) % len(statuses)]
+        pas = possible_actions_from_json(c["possible_actions"])
+        if len(pas) == 1:
+            want.append(pas[0].simulator_key)
+        else:
+            want.append(pas[agent.act(RLPolicyObservation(bs, c["request"], pas), 0.0)].simulator_key)
+        pols.append(PackedRLPolicy(agent, cfg, tables))
+        bss.append(bs)
+        reqs.append(c["request"])
+    single = [p.choice_turn_start(b, r) for p, b, r in zip(pols, bss, reqs)]
+    assert single == want
+    assert PackedRLPolicy.choice_batch(pols, bss, reqs) == want
