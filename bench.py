@@ -371,11 +371,32 @@ def b200_arm(args, rank, local_rank, world):
         te = max_over_ranks(time.perf_counter() - te0)
         barrier()
         assert a.shape == (B,)
-        e2e = {"value": B * world * args.steps / te, "unit": UNIT, "h2d_bytes_per_step": B * 144,
-               "d2h_bytes_per_step": B * A * 4 + B * 4, "ms_per_step": te / args.steps * 1e3,
-               "api": "AgentVal.act_batch(packed records) -> int32 actions; includes the copy of the records into "
-                      "pinned staging, H2D, the fused kernel (features materialised in HBM), D2H of Q and actions, "
-                      "stream synchronise"}
+        # the same work with two calls in flight (DecisionPipeline: what a lock-step driver over two groups of battles
+        # does): every step still packs its records into pinned staging, moves them to the device, runs the fused
+        # kernel with features materialised, and reads Q and actions back on the host
+        from pokeai_b200 import DecisionPipeline
+        pipe = DecisionPipeline(agent, B, depth=2)
+        for a2 in pipe.map(host_recs[i % n_rot] for i in range(max(3, min(args.warmup, 10)))):
+            pass
+        assert np.array_equal(a2, agent.act_batch(host_recs[(max(3, min(args.warmup, 10)) - 1) % n_rot]))
+        torch.cuda.synchronize()
+        barrier()
+        tp0 = time.perf_counter()
+        for a2 in pipe.map(host_recs[i % n_rot] for i in range(args.steps)):
+            pass
+        torch.cuda.synchronize()
+        tp = max_over_ranks(time.perf_counter() - tp0)
+        barrier()
+        assert a2.shape == (B,)
+        pipe.close()
+        e2e = {"value": B * world * args.steps / tp, "unit": UNIT, "h2d_bytes_per_step": B * 144,
+               "d2h_bytes_per_step": B * A * 4 + B * 4, "ms_per_step": tp / args.steps * 1e3,
+               "api": "DecisionPipeline(agent, depth=2).map(batches of packed host records) -> int32 actions per batch; "
+                      "every step copies its records into pinned staging, the kernel reads them over PCIe (zero-copy "
+                      "H2D), features are materialised in HBM, Q and actions land in pinned host memory and are copied "
+                      "out; two steps in flight",
+               "sync_value": B * world * args.steps / te, "sync_ms_per_step": te / args.steps * 1e3,
+               "sync_api": "AgentVal.act_batch(packed records): the same, one blocking call per step"}
     sampler.stop()
 
     cpu = None

@@ -236,6 +236,15 @@ PK_API int pk_session_use_prepared(pk_session* s, const float* prepared_dev, int
 PK_API int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
                            float temperature, const float* u_explore_host, const float* u_pick_host,
                            float* q_host, int32_t* action_host);
+/* The same without the final synchronise: work is queued on the session's stream and the call returns; q_host /
+ * action_host are valid after pk_session_wait.  Two sessions used alternately keep two batches in flight (the
+ * lock-step driver of SURVEY.md 8 f2: one group of battles is stepped on the host while the other is decided).
+ * Host buffers must stay untouched between submit and wait; pageable buffers are accepted but make the copies
+ * synchronous. */
+PK_API int pk_session_submit_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
+                           float temperature, const float* u_explore_host, const float* u_pick_host,
+                           float* q_host, int32_t* action_host);
+PK_API int pk_session_wait(pk_session* s);
 /* packed_host[B] -> feat_host (B, C, A), mask_host (B, A): host-buffer FeatureExtractor.transform
  * (feature_extractor.py:40-52).  Needs a session created with materialise_features != 0. */
 PK_API int pk_session_encode_host(pk_session* s, const pk_obs* packed_host, int B, float* feat_host,

@@ -85,6 +85,8 @@ _SIGNATURES = {
     "pk_session_load_weights": (C.c_int, [_vp, C.POINTER(pk_mlp)]),
     "pk_session_use_prepared": (C.c_int, [_vp, _vp, _i, _i]),
     "pk_session_decide_host": (C.c_int, [_vp, _vp, _i, _i, _f, _f, _vp, _vp, _vp, _vp]),
+    "pk_session_submit_host": (C.c_int, [_vp, _vp, _i, _i, _f, _f, _vp, _vp, _vp, _vp]),
+    "pk_session_wait": (C.c_int, [_vp]),
     "pk_session_encode_host": (C.c_int, [_vp, _vp, _i, _vp, _vp]),
     "pk_session_fetch": (C.c_int, [_vp, _i, _vp, _vp]),
     "pk_session_features": (_vp, [_vp]),

@@ -539,12 +539,31 @@ static void* pk_pinned_alias(const void* host) {
   return at.devicePointer;
 }
 
+extern "C" int pk_session_wait(pk_session* s) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(s != nullptr, "pk_session_wait: null session");
+  PK_CUDA(cudaStreamSynchronize(s->stream));
+  return PK_OK;
+}
+
 extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
                                       float temperature, const float* u_explore_host, const float* u_pick_host,
                                       float* q_host, int32_t* action_host) {
+  int rc = pk_session_submit_host(s, packed_host, B, mode, eps, temperature, u_explore_host, u_pick_host, q_host,
+                                  action_host);
+  if (rc) return rc;
+  return pk_session_wait(s);
+}
+
+// Everything pk_session_decide_host does except the final synchronise: the copies and the kernel are queued on the
+// session's stream and the call returns.  A driver with two sessions keeps two batches in flight (one being packed /
+// read on the host while the other runs); results are valid after pk_session_wait.
+extern "C" int pk_session_submit_host(pk_session* s, const pk_obs* packed_host, int B, int mode, float eps,
+                                      float temperature, const float* u_explore_host, const float* u_pick_host,
+                                      float* q_host, int32_t* action_host) {
   PK_CHECK_INIT();
-  PK_REQUIRE(s != nullptr && packed_host != nullptr, "pk_session_decide_host: null argument");
-  PK_REQUIRE(s->prepared != nullptr, "pk_session_decide_host: no weights loaded");
+  PK_REQUIRE(s != nullptr && packed_host != nullptr, "pk_session_submit_host: null argument");
+  PK_REQUIRE(s->prepared != nullptr, "pk_session_submit_host: no weights loaded");
   PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
   if (B == 0) return PK_OK;
   // Zero-copy: when the caller's buffers are pinned the kernel reads the records over PCIe itself (each is read once,
@@ -589,7 +608,6 @@ extern "C" int pk_session_decide_host(pk_session* s, const pk_obs* packed_host, 
     PK_CUDA(cudaMemcpyAsync(q_host, s->d_q, (size_t)B * s->A * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
   if (action_host && !act_direct)
     PK_CUDA(cudaMemcpyAsync(action_host, s->d_action, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
-  PK_CUDA(cudaStreamSynchronize(s->stream));
   return PK_OK;
 }
 

@@ -106,6 +106,25 @@ class DecisionSession:
             self._pin_q.data_ptr(), self._pin_action.data_ptr()))
         return self.q[:B], self.action[:B]
 
+    def submit(self, B: int, mode: int = N.PK_SELECT_ARGMAX, eps: float = 0.0, temperature: float = 1.0) -> None:
+        """Queue the first B staged records on the session's stream and return at once (pk_session_submit_host).
+        The staging and result buffers must not be touched until `wait`."""
+        if not 0 <= B <= self.max_batch:
+            raise ValueError(f"batch {B} exceeds the session capacity {self.max_batch}")
+        N.check(N.lib().pk_session_submit_host(
+            self._h, self._pin_packed.data_ptr(), B, int(mode), float(eps), float(temperature),
+            self._pin_u.data_ptr(), self._pin_u.data_ptr() + 4 * self.max_batch,
+            self._pin_q.data_ptr(), self._pin_action.data_ptr()))
+        self._pending = B
+
+    def wait(self) -> Tuple[np.ndarray, np.ndarray]:
+        """Block until the submitted batch is done; views (q (B, A), action (B,)) as `decide` returns them."""
+        B = self.__dict__.pop("_pending", None)
+        if B is None:
+            raise RuntimeError("wait() without a submitted batch")
+        N.check(N.lib().pk_session_wait(self._h))
+        return self.q[:B], self.action[:B]
+
     def encode(self, B: int) -> Tuple[np.ndarray, np.ndarray]:
         """Encode the first B staged records: (feat (B, C, A) fp32, mask (B, A) int32) host arrays."""
         if not self.materialise:
@@ -128,3 +147,80 @@ class DecisionSession:
         mask = np.empty((B, self.A), dtype=np.int32)
         N.check(N.lib().pk_session_fetch(self._h, B, feat.ctypes.data, mask.ctypes.data))
         return feat, mask
+
+
+class DecisionPipeline:
+    """`depth` decision sessions used in rotation, so that a lock-step driver over several groups of battles
+     keeps `depth` batches in flight: while one batch runs on the GPU the host packs the next and reads
+    the previous one's actions.  Greedy decisions (AgentVal semantics: q[mask == 0] = -inf, argmax).
+
+        pipe = DecisionPipeline(agent, max_batch=4096)
+        for actions in pipe.map(batches):        # batches: iterable of observation lists / packed record arrays
+            ...                                   # actions: np.int32 (B,), in submission order
+
+    or by hand: `submit(batch)` ... `result()` (first in, first out; at most `depth` outstanding)."""
+
+    def __init__(self, agent, max_batch: int, depth: int = 2, materialise_features: bool = True):
+        if depth < 1:
+            raise ValueError("depth must be >= 1")
+        self.agent = agent
+        fe = agent._feature_extractor
+        self._fe = fe
+        device = fe.session(1).device
+        self._sessions = [DecisionSession(max_batch, fe.output_dim, device, materialise_features) for _ in range(depth)]
+        self._head = 0      # next session to submit on
+        self._inflight = 0  # submitted, not yet collected
+        self._prep = None
+        self._version = None
+
+    def _point_weights(self) -> None:
+        m = self.agent._model
+        ps = list(m.parameters()) + list(m.buffers())
+        version = tuple(p._version for p in ps) + tuple(p.data_ptr() for p in ps)
+        if version == self._version:
+            return
+        for s in self._sessions:  # batches in flight still read the old weights: let them finish first
+            N.check(N.lib().pk_session_wait(s._h))
+        if hasattr(m, "prepared"):
+            prep = m.prepared(self._sessions[0].device)
+            for s in self._sessions:
+                s.use_prepared(prep, m.n_layers, m.n_channels)
+            self._prep = prep
+        else:
+            for s in self._sessions:
+                s.load_model(m)
+        self._version = version
+
+    def submit(self, obs_list) -> None:
+        if self._inflight == len(self._sessions):
+            raise RuntimeError("pipeline full: collect a result() first")
+        self._point_weights()
+        s = self._sessions[self._head]
+        n = len(obs_list)
+        if n > s.max_batch:
+            raise ValueError(f"batch {n} exceeds the pipeline capacity {s.max_batch}")
+        self._fe.pack(obs_list, out=s.packed)
+        s.submit(n)
+        self._head = (self._head + 1) % len(self._sessions)
+        self._inflight += 1
+
+    def result(self, with_q: bool = False):
+        """Actions (and Q, -inf NOT applied) of the oldest outstanding batch; copies, safe to keep."""
+        if self._inflight == 0:
+            raise RuntimeError("nothing submitted")
+        s = self._sessions[(self._head - self._inflight) % len(self._sessions)]
+        q, a = s.wait()
+        self._inflight -= 1
+        return (q.copy(), a.copy()) if with_q else a.copy()
+
+    def map(self, batches):
+        for batch in batches:
+            if self._inflight == len(self._sessions):
+                yield self.result()
+            self.submit(batch)
+        while self._inflight:
+            yield self.result()
+
+    def close(self) -> None:
+        for s in self._sessions:
+            s.close()

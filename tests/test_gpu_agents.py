@@ -126,3 +126,48 @@ def test_agent_train_follows_the_reference_rng_stream(tables):
     assert items[0].action == want[0] and items[0].reward == pytest.approx(0.1)
     assert bytes(items[0].next_state.tobytes()) == bytes(items[1].state.tobytes())
     assert np.array_equal(items[3].action_mask, mo[3])
+
+
+def test_decision_pipeline_matches_blocking_calls(tables):
+    """DecisionPipeline (pk_session_submit_host / pk_session_wait, two or three batches in flight) returns, in
+    submission order, exactly what blocking act_batch calls return; ragged batch sizes; weight change mid-stream"""
+    from pokeai_b200 import AgentVal, DecisionPipeline, FeatureExtractor, MLPModel
+    from pokeai_b200.packed import synth_packed
+    fe = FeatureExtractor(6)
+    torch.manual_seed(3)
+    model = MLPModel(fe.input_shape, fe.output_dim, n_layers=2, n_channels=64).to("cuda:0")
+    agent = AgentVal(model, fe)
+    sizes = [512, 1, 300, 512, 17, 128, 511]
+    batches = [synth_packed(n, seed=40 + i, party_size=6, kind="ragged", tables=tables) for i, n in enumerate(sizes)]
+    want = [agent.act_batch(b) for b in batches]
+    wq = [agent.q_and_action_batch(b)[0].copy() for b in batches]
+    for depth in (1, 2, 3):
+        pipe = DecisionPipeline(agent, 512, depth=depth)
+        got = list(pipe.map(batches))
+        assert len(got) == len(want) and all(np.array_equal(g, w) for g, w in zip(got, want)), depth
+        # by hand, with Q
+        pipe.submit(batches[2])
+        if depth > 1:
+            pipe.submit(batches[4])
+        else:
+            with pytest.raises(RuntimeError):
+                pipe.submit(batches[4])
+        q, a = pipe.result(with_q=True)
+        assert np.array_equal(a, want[2]) and np.array_equal(q, wq[2])
+        if depth > 1:
+            assert np.array_equal(pipe.result(), want[4])
+        with pytest.raises(RuntimeError):
+            pipe.result()
+        with pytest.raises(ValueError):
+            pipe.submit(synth_packed(513, seed=1, party_size=6, kind="full", tables=tables))
+        pipe.close()
+    # new weights while a batch is in flight: the batch in flight keeps the old ones, the next one sees the new
+    pipe = DecisionPipeline(agent, 512, depth=2)
+    pipe.submit(batches[0])
+    with torch.no_grad():
+        model.output.weight.mul_(-1.0)
+    pipe.submit(batches[0])
+    a_old, a_new = pipe.result(), pipe.result()
+    assert np.array_equal(a_old, want[0])
+    assert np.array_equal(a_new, agent.act_batch(batches[0])) and not np.array_equal(a_new, a_old)
+    pipe.close()
