@@ -129,7 +129,8 @@ class AgentVal(Agent):
         super().__init__(model, feature_extractor)
 
     def act(self, obs: object, reward: float) -> int:
-        q, a = self.q_and_action_batch([obs])
+        # a (1,) packed record (protocol.pack_request) is taken as it is
+        q, a = self.q_and_action_batch(obs if isinstance(obs, np.ndarray) else [obs])
         action = int(a[0])
         if logger.isEnabledFor(logging.DEBUG):
             n_act = int(obs["n_act"][0]) if isinstance(obs, np.ndarray) else len(obs.possible_actions)
@@ -155,7 +156,7 @@ class AgentTrain(Agent):
         seeded run makes the same explore/exploit choices as the reference."""
         n = 1
         s = self._session(n)
-        self._feature_extractor.pack([obs], out=s.packed)
+        self._feature_extractor.pack(obs if isinstance(obs, np.ndarray) else [obs], out=s.packed)
         packed = s.packed[0].copy()
         n_act = int(packed["n_act"])
         action_mask = np.zeros((self._feature_extractor.output_dim,), dtype=np.int32)

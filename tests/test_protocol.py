@@ -138,13 +138,14 @@ def test_policy_rewards_and_single_choice(cases, statuses, tables):
 
 
 @pytest.mark.gpu
-def test_policy_on_gpu_matches_object_route(cases, statuses, tables, dev):
+def test_policy_on_gpu_matches_object_route(cases, statuses, tables):
     """PackedRLPolicy (single calls and choice_batch) picks what AgentVal.act picks on the reference-style
     observation objects"""
     import torch
     from pokeai_b200 import AgentVal, FeatureExtractor, MLPModel
     from pokeai_b200.observation import RLPolicyObservation, possible_actions_from_json
     from pokeai_b200.protocol import PackedRLPolicy
+    dev = torch.device("cuda:0")
     sel = [c for c in cases if c["party_size"] == 6][:64]
     fe = FeatureExtractor(6)
     torch.manual_seed(5)
