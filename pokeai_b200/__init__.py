@@ -10,7 +10,7 @@ __version__ = "0.1.0"
 _LAZY = {
     "FeatureExtractor": ".feature_extractor", "MLPModel": ".mlp_model", "Agent": ".agent", "AgentVal": ".agent",
     "AgentTrain": ".agent", "ReplayBuffer": ".replay_buffer", "ReplayBufferItem": ".replay_buffer",
-    "Trainer": ".trainer", "DQN_DEFAULT_PARAMS": ".trainer", "DecisionSession": ".session", "DecisionPipeline": ".session",
+    "Trainer": ".trainer", "DQN_DEFAULT_PARAMS": ".trainer", "DecisionSession": ".session", "DecisionPipeline": ".session", "pinned_records": ".session",
     "PartyEvaluator": ".party_evaluator", "PartyEvaluatorQuick": ".party_evaluator",
     "PackedRLPolicy": ".protocol", "pack_request": ".protocol", "pack_requests": ".protocol",
 }

@@ -96,7 +96,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
   g.hidden_tc = env_int("PK_HIDDEN_TC", 0, 0, 1);  // 64-channel hidden layers on the 3xTF32 mma.sync path (measured: no gain)
   g.pdl = env_int("PK_PDL", 1, 0, 1);
-  g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 1);
+  g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 2);
   g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   return PK_OK;
@@ -574,7 +574,8 @@ extern "C" int pk_session_submit_host(pk_session* s, const pk_obs* packed_host, 
   int32_t* act_dev = s->d_action;
   bool q_direct = false, act_direct = false;
   if (g.zero_copy) {
-    if (void* p = pk_pinned_alias(packed_host)) in_dev = static_cast<const pk_obs*>(p);
+    if (g.zero_copy == 1)  // 2 = results only: the records go through the copy engine, which overlaps another stream's kernel
+      if (void* p = pk_pinned_alias(packed_host)) in_dev = static_cast<const pk_obs*>(p);
     if (void* p = pk_pinned_alias(q_host)) {
       q_dev = static_cast<float*>(p);
       q_direct = true;

@@ -106,13 +106,21 @@ class DecisionSession:
             self._pin_q.data_ptr(), self._pin_action.data_ptr()))
         return self.q[:B], self.action[:B]
 
-    def submit(self, B: int, mode: int = N.PK_SELECT_ARGMAX, eps: float = 0.0, temperature: float = 1.0) -> None:
+    def submit(self, B: int, mode: int = N.PK_SELECT_ARGMAX, eps: float = 0.0, temperature: float = 1.0,
+               packed: Optional[np.ndarray] = None) -> None:
         """Queue the first B staged records on the session's stream and return at once (pk_session_submit_host).
-        The staging and result buffers must not be touched until `wait`."""
+        The staging and result buffers must not be touched until `wait`.  `packed`: read the records from this
+        caller-owned array instead of the staging buffer (no host copy when it is pinned, see `pinned_records`)."""
         if not 0 <= B <= self.max_batch:
             raise ValueError(f"batch {B} exceeds the session capacity {self.max_batch}")
+        src = self._pin_packed.data_ptr()
+        if packed is not None:
+            if packed.dtype != PK_OBS_DTYPE or not packed.flags.c_contiguous or len(packed) < B:
+                raise ValueError("packed must be a C-contiguous PK_OBS_DTYPE array of at least B records")
+            src = packed.ctypes.data
+            self._keep = packed
         N.check(N.lib().pk_session_submit_host(
-            self._h, self._pin_packed.data_ptr(), B, int(mode), float(eps), float(temperature),
+            self._h, src, B, int(mode), float(eps), float(temperature),
             self._pin_u.data_ptr(), self._pin_u.data_ptr() + 4 * self.max_batch,
             self._pin_q.data_ptr(), self._pin_action.data_ptr()))
         self._pending = B
@@ -123,6 +131,7 @@ class DecisionSession:
         if B is None:
             raise RuntimeError("wait() without a submitted batch")
         N.check(N.lib().pk_session_wait(self._h))
+        self._keep = None
         return self.q[:B], self.action[:B]
 
     def encode(self, B: int) -> Tuple[np.ndarray, np.ndarray]:
@@ -147,6 +156,14 @@ class DecisionSession:
         mask = np.empty((B, self.A), dtype=np.int32)
         N.check(N.lib().pk_session_fetch(self._h, B, feat.ctypes.data, mask.ctypes.data))
         return feat, mask
+
+
+def pinned_records(n: int) -> np.ndarray:
+    """(n,) zeroed PK_OBS_DTYPE records in page-locked host memory: a driver packs its requests straight into such an
+    array (`protocol.pack_requests`-style field writes, or a byte copy) and hands it to `DecisionPipeline.submit(...,
+    pinned=True)`, so the records cross PCIe once, read by the kernel, with no staging copy."""
+    t = torch.zeros((int(n), PK_OBS_BYTES), dtype=torch.uint8).pin_memory()
+    return t.numpy().reshape(-1).view(PK_OBS_DTYPE)  # the view keeps the tensor alive
 
 
 class DecisionPipeline:
@@ -175,8 +192,11 @@ class DecisionPipeline:
 
     def _point_weights(self) -> None:
         m = self.agent._model
-        ps = list(m.parameters()) + list(m.buffers())
-        version = tuple(p._version for p in ps) + tuple(p.data_ptr() for p in ps)
+        ps = self.__dict__.get("_plist")
+        if ps is None or self._plist_model is not m:
+            ps = self._plist = list(m.parameters()) + list(m.buffers())
+            self._plist_model = m
+        version = [p._version for p in ps] + [p.data_ptr() for p in ps]
         if version == self._version:
             return
         for s in self._sessions:  # batches in flight still read the old weights: let them finish first
@@ -191,7 +211,9 @@ class DecisionPipeline:
                 s.load_model(m)
         self._version = version
 
-    def submit(self, obs_list) -> None:
+    def submit(self, obs_list, pinned: bool = False) -> None:
+        """`pinned=True`: `obs_list` is a record array from `pinned_records` that the caller leaves untouched until
+        the matching `result()`; the kernel reads it in place and no staging copy is made."""
         if self._inflight == len(self._sessions):
             raise RuntimeError("pipeline full: collect a result() first")
         self._point_weights()
@@ -199,8 +221,11 @@ class DecisionPipeline:
         n = len(obs_list)
         if n > s.max_batch:
             raise ValueError(f"batch {n} exceeds the pipeline capacity {s.max_batch}")
-        self._fe.pack(obs_list, out=s.packed)
-        s.submit(n)
+        if pinned:
+            s.submit(n, packed=obs_list)
+        else:
+            self._fe.pack(obs_list, out=s.packed)
+            s.submit(n)
         self._head = (self._head + 1) % len(self._sessions)
         self._inflight += 1
 
@@ -213,11 +238,11 @@ class DecisionPipeline:
         self._inflight -= 1
         return (q.copy(), a.copy()) if with_q else a.copy()
 
-    def map(self, batches):
+    def map(self, batches, pinned: bool = False):
         for batch in batches:
             if self._inflight == len(self._sessions):
                 yield self.result()
-            self.submit(batch)
+            self.submit(batch, pinned)
         while self._inflight:
             yield self.result()
 

@@ -161,6 +161,21 @@ def test_decision_pipeline_matches_blocking_calls(tables):
         with pytest.raises(ValueError):
             pipe.submit(synth_packed(513, seed=1, party_size=6, kind="full", tables=tables))
         pipe.close()
+    # records handed over in pinned memory: read in place, same results; pageable arrays passed as "pinned" still work
+    from pokeai_b200 import pinned_records
+    pipe = DecisionPipeline(agent, 512, depth=2)
+    pins = []
+    for bt in batches:
+        p_ = pinned_records(len(bt))
+        p_.view(np.uint8)[...] = bt.view(np.uint8)
+        pins.append(p_)
+    got = list(pipe.map(pins, pinned=True))
+    assert all(np.array_equal(g, w) for g, w in zip(got, want))
+    got = list(pipe.map(batches, pinned=True))
+    assert all(np.array_equal(g, w) for g, w in zip(got, want))
+    with pytest.raises(ValueError):
+        pipe.submit(np.zeros(4, dtype=np.uint8), pinned=True)
+    pipe.close()
     # new weights while a batch is in flight: the batch in flight keeps the old ones, the next one sees the new
     pipe = DecisionPipeline(agent, 512, depth=2)
     pipe.submit(batches[0])

@@ -28,3 +28,18 @@ for B in (64, 4096, 65536):
         s.decide(B)
     td = (time.perf_counter() - t2) / n
     print(f"B={B}: act_batch {dt*1e6:.1f} us ({B/dt/1e6:.2f} M decisions/s); staging copy {tp*1e6:.1f} us; session.decide {td*1e6:.1f} us; env PK_ZERO_COPY={os.environ.get('PK_ZERO_COPY','1')}")
+    from pokeai_b200 import DecisionPipeline
+    for depth in (1, 2, 3, 4):
+        pipe = DecisionPipeline(agent, B, depth=depth)
+        for _ in pipe.map(recs[i % 4] for i in range(8)):
+            pass
+        t3 = time.perf_counter()
+        for _ in pipe.map(recs[i % 4] for i in range(n)):
+            pass
+        tq = (time.perf_counter() - t3) / n
+        pipe.close()
+        print(f"   pipeline depth {depth}: {tq*1e6:.1f} us per batch ({B/tq/1e6:.2f} M decisions/s)")
+    t4 = time.perf_counter()
+    for i in range(n):
+        s.submit(B); s.wait()
+    print(f"   submit+wait without the staging copy: {(time.perf_counter()-t4)/n*1e6:.1f} us; result copy {B*40/1e3:.0f} KB")
