@@ -14,8 +14,11 @@ states (battles are independent; no data-path collective) => weak scaling.
 Prints ONE JSON line (rank 0).  Keys beyond the base contract:
   roofline      achieved HBM GB/s of the decision kernel = algorithmic bytes per launch
                 (22 432 B per decision) / CUDA-event time per launch.
-  e2e           the same metric through the host-buffer public API (AgentVal.act_batch): pinned
-                host records -> H2D -> kernel -> D2H of Q and actions -> synchronise, every step.
+  e2e           the same metric through the host-buffer public API, every step moving its records host ->
+                device and its Q + actions device -> host: `value` = DecisionPipeline (three steps in flight,
+                records in pinned host memory read by the kernel over PCIe); `pageable_input_value` = the same
+                from ordinary host memory (one more host copy per step); `sync_value` = one blocking
+                AgentVal.act_batch call per step.
   cpu_baseline  the reference algorithm's CPU path (oracle port of the reference's Python,
                 oracle/ref_port.py) timed on this box's host cores on the same states.
   clocks        SM clock / throttle reasons sampled through NVML during the timed region.
