@@ -121,6 +121,41 @@ def test_encode_full_size_properties(tables, dev):
     assert np.array_equal(bits(f[torch.from_numpy(idx).to(dev)].cpu().numpy()), bits(fo))
 
 
+def test_decide_full_size_properties(tables, dev):
+    """65536 states through the fused kernel (BASELINE configs[2]): with and without materialised features the Q
+    values are the same bits; the action is the exact masked argmax of the kernel's own Q; the dense-input kernel on
+    the materialised features agrees; 1024 sampled battles agree with the oracle; a second launch is bit-identical"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import ops
+    from pokeai_b200.packed import synth_packed
+    B, A, nl, H = 65536, 9, 2, 64
+    rec = synth_packed(B, seed=123, party_size=6, kind="ragged", tables=tables)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=5)
+    prepared = ops.prepare_weights(sd, dev)[0]
+    pk = _to_dev(rec, dev)
+    f, m, q, a = ops.decide(pk, A, prepared, nl, H)
+    _, m2, q2, a2 = ops.decide(pk, A, prepared, nl, H, materialise=False)
+    assert torch.equal(m, m2) and torch.equal(a, a2)
+    # the two kernels (one / two battles per warp) order their sums differently: close, not identical
+    assert float((q - q2).abs().max()) < 2e-5
+    f3, m3, q3, a3 = ops.decide(pk, A, prepared, nl, H)
+    assert torch.equal(q, q3) and torch.equal(a, a3) and torch.equal(f.view(torch.int32), f3.view(torch.int32))
+    n_act = torch.from_numpy(rec["n_act"].astype(np.int64)).to(dev)
+    legal = torch.arange(A, device=dev)[None, :] < n_act[:, None]
+    assert torch.equal(m.bool(), legal)
+    qm = torch.where(legal, q, torch.full_like(q, float("-inf")))
+    assert torch.equal(a.long(), qm.argmax(dim=1))
+    qd = ops.mlp_forward(prepared, nl, H, f)
+    assert float((qd - q).abs().max()) < 2e-5
+    idx = np.random.default_rng(1).choice(B, 1024, replace=False)
+    fo, mo = packed_oracle.encode(rec[idx], 6, tables)
+    with torch.no_grad():
+        qo = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    ti = torch.from_numpy(idx).to(dev)
+    assert np.array_equal(bits(f[ti].cpu().numpy()), bits(fo)) and np.array_equal(m[ti].cpu().numpy(), mo)
+    np.testing.assert_allclose(q[ti].cpu().numpy(), qo, rtol=Q_RTOL, atol=Q_ATOL)
+
+
 # ---------------------------------------------------------------------------------------------
 # forward
 # ---------------------------------------------------------------------------------------------

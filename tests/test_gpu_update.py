@@ -130,6 +130,47 @@ def test_update_is_deterministic_and_shards_add_up(tables):
     assert abs(float((la + lb).item()) - float(l1.item())) < 1e-6
 
 
+def test_update_full_size_properties(tables):
+    """32768 transitions (BASELINE configs[3]): bit-identical run to run; eight contiguous shards with n_global =
+    32768 sum to the full-batch gradient and loss (the data-parallel invariant at the benchmark's size); 256 sampled
+    transitions agree with the oracle's per-sample gradient sum through linearity (their shard alone, n_global kept)"""
+    from oracle import ref_port
+    from pokeai_b200 import ops
+    n, ps, nl, H, A = 32768, 6, 2, 64, 9
+    rec_s, rec_n, action, reward, terminal = _synth_transitions(n, ps, tables, seed=21)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=22)
+    sd_t = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=23)
+    prepared = ops.prepare_weights(sd, DEV)[0]
+    prepared_t = ops.prepare_weights(sd_t, DEV)[0]
+    full = _dev_batch(rec_s, rec_n, action, reward, terminal)
+    g1, l1 = ops.dqn_grad(prepared, prepared_t, nl, H, A, *full, gamma=0.95)
+    g2, l2 = ops.dqn_grad(prepared, prepared_t, nl, H, A, *full, gamma=0.95)
+    assert torch.equal(g1, g2) and torch.equal(l1, l2)
+    assert bool(torch.isfinite(g1).all()) and float(g1.abs().max()) > 0
+    gs, ls = torch.zeros_like(g1), 0.0
+    for r in range(8):
+        lo, hi = n * r // 8, n * (r + 1) // 8
+        g, l = ops.dqn_grad(prepared, prepared_t, nl, H, A, *[t[lo:hi].contiguous() for t in full], gamma=0.95, n_global=n)
+        gs += g
+        ls += float(l.item())
+    np.testing.assert_allclose(gs.cpu().numpy(), g1.cpu().numpy(), rtol=2e-4, atol=2e-7)
+    assert abs(ls - float(l1.item())) < 1e-5
+    # a 256-transition slice against the oracle, scaled by its share of the global batch
+    lo, hi = 5000, 5256
+    g, l = ops.dqn_grad(prepared, prepared_t, nl, H, A, *[t[lo:hi].contiguous() for t in full], gamma=0.95, n_global=n)
+    from oracle import packed_oracle
+    fs, _ = packed_oracle.encode(rec_s[lo:hi], ps, tables)
+    fn, mn = packed_oracle.encode(rec_n[lo:hi], ps, tables)
+    loss_o, grads_o = ref_port.dqn_update_grads(sd, sd_t, fs, action[lo:hi], reward[lo:hi], fn, mn, ~terminal[lo:hi], 0.95,
+                                                double_dqn=True)
+    scale = (hi - lo) / n  # the oracle averages over its 256 transitions, the kernel divides by n_global
+    gmax = max(float(t.abs().max()) for t in grads_o.values()) * scale
+    for k, t in ops.unflatten(g, nl, H, tables.n_channels).items():
+        np.testing.assert_allclose(t.cpu().numpy(), grads_o[k].numpy() * scale, rtol=G_RTOL, atol=max(1e-9, 1e-6 * gmax),
+                                   err_msg=k)
+    assert abs(float(l.item()) - loss_o * scale) < 1e-7
+
+
 def test_update_bad_arguments(tables):
     from pokeai_b200 import _native as N
     from pokeai_b200 import ops
