@@ -223,6 +223,22 @@ PK_API int pk_clamp_adam(float* params, const float* grad, float* exp_avg, float
                   int n_channels, int in_channels, float lr, float beta1, float beta2, float eps, int step,
                   float* prepared, void* stream);
 
+/* Data-parallel form of pk_clamp_adam: gradient sum over ranks + clamp + Adam in ONE kernel over NVLink peer memory
+ * (replaces dist.all_reduce(grad) + the clamp / optimizer.step of trainer.py:193-195 at world size > 1).
+ * peer_grads[r] (r < world): device pointer, valid in THIS process, to rank r's gradient buffer for this epoch:
+ * n_params floats (pre-clamp, as pk_dqn_grad writes them) followed by one float, the rank's loss share.
+ * peer_flags[r]: rank r's flag words (>= world uint32, zero before the first call), mapped the same way.
+ * epoch: 1, 2, 3, ... the same on every rank; buffers must alternate between two sets by epoch parity (a rank may
+ * overwrite the set of epoch e only after its own call for epoch e + 1).  Every rank of the job must make the call.
+ * grad_sum (n_params floats, may be NULL) receives the reduced pre-clamp gradient; loss_status (2 floats, may be
+ * NULL): [0] = sum of the loss shares, [1] = 1.0 if a peer did not arrive within ~2 s (the step is then invalid).
+ * The sum runs in rank order on every rank: identical bits everywhere. */
+#define PK_MAX_PEERS 8
+PK_API int pk_peer_clamp_adam(float* params, const float* const* peer_grads, uint32_t* const* peer_flags, int rank,
+                       int world, uint32_t epoch, float* exp_avg, float* exp_avg_sq, int n_layers, int n_channels,
+                       int in_channels, float lr, float beta1, float beta2, float eps, int step, float* prepared,
+                       float* grad_sum, float* loss_status, void* stream);
+
 /* ---- host-buffer session (for non-torch callers, and the end-to-end measurement) ------
  * Owns device buffers for up to max_batch observations and one stream.  *_host calls copy
  * packed observations host->device, run pk_decide, copy q / action back and synchronise. */

@@ -347,6 +347,82 @@ __global__ void pk_dqn_flat_kernel(const float* __restrict__ gsum, PkParamLayout
 struct PkAdam {
   float one_minus_b1, b2, one_minus_b2, step_size, bc2_sqrt, eps;
 };
+// ---- gradient exchange over NVLink peer memory, fused with clamp + Adam ----------------------------------------------
+// The data-parallel update has one exchange: the sum over ranks of the flat gradient, followed by the
+// clamp and the Adam step on every rank.  NCCL does it as allreduce -> separate kernel; for the default network the
+// vector is 175 KB, so the step is pure latency.  Here ONE kernel does both: every rank's gradient lives in a buffer
+// that all peers have mapped (torch symmetric memory = cuMem handles exchanged once; NVSwitch gives every GPU a direct
+// path to every peer), a flag per rank says "my gradient of epoch e is complete", and each thread loads its element
+// from all W peers IN RANK ORDER, sums, clamps and applies Adam.  The fixed order makes the reduced gradient and the
+// updated weights bit-identical on every rank (NCCL's ring / tree order is not specified).
+// Protocol: gradients are double-buffered by epoch parity.  Publishing epoch e+1 happens after this rank's epoch-e
+// kernel finished (stream order), i.e. after it stopped reading the peers' parity-e buffers, so a peer that has seen
+// every flag reach e+1 may overwrite its parity-e buffer for epoch e+2: one flag round per step, no second barrier.
+// A rank that never arrives would spin the others for ever: the wait gives up after ~2 s and raises status[0].
+__device__ __forceinline__ unsigned long long pk_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+struct PkPeers {
+  const float* grad[PK_MAX_PEERS];  // every rank's gradient buffer of this epoch's parity, (n + 1) floats: gradient, loss share
+  unsigned* flags[PK_MAX_PEERS];    // every rank's flag words; flags[d][r] = last epoch rank r published to rank d
+  int rank, world;
+  unsigned epoch;
+};
+__device__ __forceinline__ unsigned pk_ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float pk_ld_relaxed_sys(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe, float* __restrict__ m,
+                                          float* __restrict__ v, PkParamLayout P, PkLayout lay, PkAdam h,
+                                          float* __restrict__ prepared, float* __restrict__ grad_sum,
+                                          float* __restrict__ loss_status) {
+  if (blockIdx.x == 0 && threadIdx.x < pe.world) {  // publish: this rank's gradient was written by earlier kernels
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pe.flags[threadIdx.x] + pe.rank), "r"(pe.epoch) : "memory");
+  }
+  if (threadIdx.x < pe.world) {  // every CTA waits on this rank's own flag words (local memory)
+    const unsigned* f = pe.flags[pe.rank] + threadIdx.x;
+    const unsigned long long t0 = pk_globaltimer();
+    while ((int)(pk_ld_acquire_sys(f) - pe.epoch) < 0) {
+      if (pk_globaltimer() - t0 > 2000000000ull) {
+        if (loss_status != nullptr) loss_status[1] = 1.0f;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > P.total) return;
+  float gs = 0.0f;
+  for (int r = 0; r < pe.world; ++r) gs += pk_ld_relaxed_sys(pe.grad[r] + i);  // rank order: same bits everywhere
+  if (i == P.total) {  // the loss shares ride in the last slot
+    if (loss_status != nullptr) loss_status[0] = gs;
+    return;
+  }
+  if (grad_sum != nullptr) grad_sum[i] = gs;
+  const float g = fminf(fmaxf(gs, -1.0f), 1.0f);                  // trainer.py:193-194, after the reduce
+  const float mi = m[i] + (g - m[i]) * h.one_minus_b1;
+  const float vi = v[i] * h.b2 + (h.one_minus_b2 * g) * g;
+  const float denom = sqrtf(vi) / h.bc2_sqrt + h.eps;
+  const float p = params[i] + (-h.step_size * mi) / denom;
+  m[i] = mi;
+  v[i] = vi;
+  params[i] = p;
+  if (prepared != nullptr) {
+    unsigned wn;
+    prepared[pk_flat_to_prepared(P, lay, i, &wn)] = p;
+    if (wn) prepared[wn] = p;
+  }
+}
+
 __global__ void pk_clamp_adam_kernel(float* __restrict__ params, const float* __restrict__ grad, float* __restrict__ m,
                                      float* __restrict__ v, PkParamLayout P, PkLayout lay, PkAdam h,
                                      float* __restrict__ prepared) {

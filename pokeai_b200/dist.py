@@ -38,3 +38,86 @@ def allreduce_sum_(grad: torch.Tensor, loss: Optional[torch.Tensor] = None, dist
     dist.all_reduce(grad, op=dist.ReduceOp.SUM)
     if loss is not None:
         dist.all_reduce(loss, op=dist.ReduceOp.SUM)
+
+
+class PeerGradExchange:
+    """Gradient sum + clamp + Adam in one kernel over NVLink peer memory (pk_peer_clamp_adam, pk_update.cuh).
+
+    Every rank's flat gradient lives in a buffer all peers have mapped (torch symmetric memory does the one-time
+    handle exchange: plumbing only); each step the ranks write their shard gradient into the buffer of the step's
+    parity and launch ONE kernel that waits on per-rank flags, sums the W copies in rank order, clamps and applies
+    Adam.  No NCCL call per step; the reduced gradient and the new weights are bit-identical on every rank.
+
+        px = PeerGradExchange.create(n_params, device)      # None when unavailable (every rank agrees)
+        grad, loss = px.next_slot()                          # views: write the shard gradient / loss share here
+        px.reduce_clamp_adam(flat, exp_avg, exp_avg_sq, n_layers, H, C, step, lr, betas, eps, prepared)
+        px.loss_status -> tensor [summed loss, timeout flag]
+    """
+
+    FLAG_FLOATS = 64  # 256 B of flag words in front of the two gradient sets
+
+    def __init__(self, n_params: int, device: torch.device, group=None):
+        import ctypes as C
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self._C = C
+        group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > 8:
+            raise RuntimeError("PeerGradExchange supports up to 8 ranks (one NVSwitch box)")
+        self.n = int(n_params)
+        self.npad = (self.n + 1 + 63) // 64 * 64
+        total = self.FLAG_FLOATS + 2 * self.npad
+        self.buf = symm.empty(total, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.hdl.barrier()  # every rank's flags are zero before anyone publishes
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        assert len(ptrs) == self.world and ptrs[self.rank] == self.buf.data_ptr()
+        self._flag_ptrs = (C.c_void_p * self.world)(*ptrs)
+        base = [p + 4 * self.FLAG_FLOATS for p in ptrs]
+        self._grad_ptrs = [(C.c_void_p * self.world)(*[b + 4 * self.npad * par for b in base]) for par in (0, 1)]
+        self.epoch = 0
+        self.loss_status = torch.zeros(2, dtype=torch.float32, device=device)
+        self.device = device
+
+    @classmethod
+    def create(cls, n_params: int, device, group=None) -> Optional["PeerGradExchange"]:
+        """Collective: every rank calls it; returns an exchange on all ranks or None on all ranks."""
+        import os
+        import torch.distributed as dist
+        device = torch.device(device)
+        px, ok = None, 1
+        if os.environ.get("PK_PEER_ALLREDUCE", "1") == "0" or device.type != "cuda" or dist.get_backend(group) != "nccl":
+            ok = 0
+        else:
+            try:
+                px = cls(n_params, device, group)
+            except Exception as e:  # no P2P mapping on this machine, older torch, ...
+                import logging
+                logging.getLogger(__name__).warning("peer gradient exchange unavailable, using NCCL allreduce: %s", e)
+                ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=device if device.type == "cuda" else "cpu")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        return px if int(flag.item()) == 1 else None
+
+    def next_slot(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Advance to the next epoch; (gradient (n,), loss share (1,)) views of this rank's buffer for it."""
+        self.epoch += 1
+        o = self.FLAG_FLOATS + (self.epoch & 1) * self.npad
+        return self.buf[o:o + self.n], self.buf[o + self.n:o + self.n + 1]
+
+    def reduce_clamp_adam(self, params: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor, n_layers: int,
+                          n_channels: int, in_channels: int, step: int, lr: float, betas, eps: float,
+                          prepared: Optional[torch.Tensor] = None, grad_sum: Optional[torch.Tensor] = None) -> None:
+        from . import _native as N
+        assert self.epoch >= 1, "next_slot() first"
+        assert params.numel() == self.n and params.is_cuda and params.dtype == torch.float32
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(N.lib().pk_peer_clamp_adam(
+            params.data_ptr(), self._grad_ptrs[self.epoch & 1], self._flag_ptrs, self.rank, self.world, self.epoch,
+            exp_avg.data_ptr(), exp_avg_sq.data_ptr(), int(n_layers), int(n_channels), int(in_channels), float(lr),
+            float(betas[0]), float(betas[1]), float(eps), int(step),
+            prepared.data_ptr() if prepared is not None else None,
+            grad_sum.data_ptr() if grad_sum is not None else None, self.loss_status.data_ptr(), stream))
