@@ -48,6 +48,9 @@ def parse_args():
     p.add_argument("--layers", type=int, default=2)
     p.add_argument("--channels", type=int, default=64)
     p.add_argument("--cpu-seconds", type=float, default=10.0)
+    p.add_argument("--allreduce", default="peer", choices=["peer", "nccl"],
+                   help="N > 1, default net: gradient exchange fused with clamp + Adam over NVLink peer memory "
+                        "(pk_peer_clamp_adam), or NCCL allreduce + pk_clamp_adam")
     return p.parse_args()
 
 
@@ -146,6 +149,10 @@ def main():
                                                 dtype=torch.float32, device=dev)
     opt = tr.optimizer
     step_no = [0]
+    px = None
+    if world > 1 and not wide_net and args.allreduce == "peer":
+        from pokeai_b200.dist import PeerGradExchange
+        px = PeerGradExchange.create(tr._flat.numel(), dev)  # None on every rank if the box cannot map peer memory
 
     def step(i):
         s, s2, a, r, t = dev_sets[i % n_rot]
@@ -155,6 +162,14 @@ def main():
                 dist.all_reduce(tr._grad, op=dist.ReduceOp.SUM)
             tr._wide_apply()
             return loss
+        if px is not None:  # shard gradient straight into the peer-mapped slot; ONE kernel: sum over ranks + clamp + Adam
+            gslot, lslot = px.next_slot()
+            ops.dqn_grad(tr._prepared, tr._prepared_target, nl, H, A, s, s2, a, r, t, tr.gamma, True, n_global=NG,
+                         scratch=scratch, out_grad=gslot, out_loss=lslot)
+            step_no[0] += 1
+            px.reduce_clamp_adam(tr._flat, opt.exp_avg, opt.exp_avg_sq, nl, H, Cn, step_no[0], opt.lr, opt.betas, opt.eps,
+                                 prepared=tr._prepared)
+            return px.loss_status[:1]
         grad, loss = ops.dqn_grad(tr._prepared, tr._prepared_target, nl, H, A, s, s2, a, r, t, tr.gamma, True,
                                   n_global=NG, scratch=scratch)
         if world > 1:
@@ -220,8 +235,13 @@ def main():
             "config": {"workload": f"DQN minibatch update, {NG} packed transitions per step (BASELINE configs[3]), "
                                    f"default MLP {nl}x{H}, Double DQN, gamma 0.95, 5% terminal",
                        "global_transitions_per_step": NG, "transitions_per_gpu": n,
-                       "sharding": f"dp{world}: contiguous shards of one global minibatch; one NCCL sum-allreduce of "
-                                   f"{tr._flat.numel()} fp32 gradients per step, clamp + Adam after the reduce",
+                       "sharding": f"dp{world}: contiguous shards of one global minibatch; " +
+                                   ("gradient sum over ranks + clamp + Adam in ONE kernel over NVLink peer memory "
+                                    f"(pk_peer_clamp_adam, {tr._flat.numel()} fp32 gradients, rank-ordered sum)"
+                                    if px is not None else
+                                    f"one NCCL sum-allreduce of {tr._flat.numel()} fp32 gradients per step, clamp + Adam "
+                                    "after the reduce"),
+                       "exchange": "peer" if px is not None else ("nccl" if world > 1 else "none"),
                        "l2": f"{n_rot} rotating transition sets; inputs are 297 B per transition (9.7 MB per set), "
                              "the kernels are compute/latency-bound, not HBM-bound"},
             "roofline": {"bound": "tensor (bf16 tcgen05 GEMMs)" if wide_net else

@@ -175,7 +175,8 @@ def prepare_from_flat(flat: torch.Tensor, n_layers: int, H: int, Cin: int, out: 
 def dqn_grad(prepared: torch.Tensor, prepared_target: torch.Tensor, n_layers: int, n_channels_: int, A: int,
              state: torch.Tensor, next_state: torch.Tensor, action: torch.Tensor, reward: torch.Tensor,
              terminal: torch.Tensor, gamma: float, double_dqn: bool = True, n_global: Optional[int] = None,
-             scratch: Optional[torch.Tensor] = None):
+             scratch: Optional[torch.Tensor] = None, out_grad: Optional[torch.Tensor] = None,
+             out_loss: Optional[torch.Tensor] = None):
     """Packed transitions (device) -> (flat pre-clamp gradient in state_dict order, loss (1,) tensor).
     state / next_state: (n, 144) uint8; action (n,) int32; reward (n,) fp32; terminal (n,) uint8."""
     dev = _dev(state)
@@ -187,8 +188,11 @@ def dqn_grad(prepared: torch.Tensor, prepared_target: torch.Tensor, n_layers: in
     lib = N.lib()
     if scratch is None:
         scratch = torch.empty(lib.pk_dqn_scratch_floats(n_layers, n_channels_, Cn, n), dtype=torch.float32, device=dev)
-    grad = torch.empty(lib.pk_mlp_param_floats(n_layers, n_channels_, Cn), dtype=torch.float32, device=dev)
-    loss = torch.zeros(1, dtype=torch.float32, device=dev)
+    n_par = lib.pk_mlp_param_floats(n_layers, n_channels_, Cn)
+    grad = out_grad if out_grad is not None else torch.empty(n_par, dtype=torch.float32, device=dev)
+    loss = out_loss if out_loss is not None else torch.zeros(1, dtype=torch.float32, device=dev)
+    assert grad.is_cuda and grad.dtype == torch.float32 and grad.is_contiguous() and grad.numel() == n_par
+    assert loss.is_cuda and loss.dtype == torch.float32 and loss.numel() == 1
     b = N.pk_batch()
     b.n, b.n_global = n, (n if n_global is None else int(n_global))
     b.state, b.next_state = state.data_ptr(), next_state.data_ptr()

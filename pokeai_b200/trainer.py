@@ -321,24 +321,43 @@ class Trainer:
         b.action, b.reward, b.terminal = base + o[2], base + o[3], base + o[4]
         stream = torch.cuda.current_stream(self.device).cuda_stream
         lib = N.lib()
-        if n == 0:  # a rank whose shard of a tiny minibatch is empty still takes part in the allreduce
-            self._grad.zero_()
-            self._loss.zero_()
-        else:
-                N.check(lib.pk_dqn_grad(self._prepared.data_ptr(), self._prepared_target.data_ptr(), self._nl, self._H,
-                                    self.feature_extractor.output_dim, C.byref(b), float(self.gamma),
-                                    1 if self.double_dqn else 0, self._grad.data_ptr(), self._loss.data_ptr(),
-                                    S["scratch"].data_ptr(), stream))
         dist = self._dist()
+        px = self._peer_exchange(dist)
+        grad, loss = (self._grad, self._loss) if px is None else px.next_slot()
+        if n == 0:  # a rank whose shard of a tiny minibatch is empty still takes part in the exchange
+            grad.zero_()
+            loss.zero_()
+        else:
+            N.check(lib.pk_dqn_grad(self._prepared.data_ptr(), self._prepared_target.data_ptr(), self._nl, self._H,
+                                    self.feature_extractor.output_dim, C.byref(b), float(self.gamma),
+                                    1 if self.double_dqn else 0, grad.data_ptr(), loss.data_ptr(),
+                                    S["scratch"].data_ptr(), stream))
+        opt = self.optimizer
+        opt.step_count += 1
+        if px is not None:  # ONE kernel over NVLink peer memory: sum over ranks (rank order) + clamp + Adam
+            px.reduce_clamp_adam(self._flat, opt.exp_avg, opt.exp_avg_sq, self._nl, self._H, self._C, opt.step_count,
+                                 opt.lr, opt.betas, opt.eps, prepared=self._prepared, grad_sum=self._grad)
+            ls = px.loss_status.tolist()
+            if ls[1] != 0.0:
+                raise RuntimeError("peer gradient exchange: a rank did not arrive within the time limit")
+            return float(ls[0])
         if dist is not None:  # sum of shard gradients == gradient of the global mean loss; clamp comes after
             from .dist import allreduce_sum_
             allreduce_sum_(self._grad, self._loss, dist)
-        opt = self.optimizer
-        opt.step_count += 1
         N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
                                   opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
                                   opt.betas[1], opt.eps, opt.step_count, self._prepared.data_ptr(), stream))
         return float(self._loss.item())
+
+    def _peer_exchange(self, dist):
+        """PeerGradExchange of the default (small) network when a NCCL group is active and the box maps peer memory;
+        created collectively on the first distributed update, None otherwise (then: NCCL allreduce)."""
+        if dist is None or self._wide:
+            return None
+        if "_px" not in self.__dict__:
+            from .dist import PeerGradExchange
+            self._px = PeerGradExchange.create(self._flat.numel(), self.device)
+        return self._px
 
     def _wide_grad_device(self, s_d, s2_d, a_d, r_d, t_d, n_global: int):
         """Device-resident part of the wide update: fills self._grad, returns the loss tensor (1,)."""

@@ -309,3 +309,18 @@ def test_trainer_all_terminal_minibatch_raises_like_the_reference(tables):
         tr._update()
     with pytest.raises(IndexError):  # replay_buffer.py:30-31
         Trainer({}, {"batch_size": 64}, {"party_size": 6})._update()
+
+
+def test_peer_gradient_exchange_two_gpus():
+    """pk_peer_clamp_adam (gradient sum over NVLink peer memory fused with clamp + Adam) against the NCCL route, one
+    process per GPU: tools/check_peer_update.py under torchrun.  Needs two GPUs; skipped on a one-GPU box."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = Path(__file__).resolve().parents[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29581", str(root / "tools" / "check_peer_update.py")],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "peer update ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
