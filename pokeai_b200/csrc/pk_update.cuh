@@ -258,13 +258,31 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
 #pragma unroll
       for (int l = 1; l < NL; ++l) {
         const float hk = Rh[(l - 1) * HP + own_k];
+        const float* dzl = Rdz + l * HP + own_j0;  // EPT adjacent channels: 16-byte loads when EPT allows
+        if constexpr (EPT % 4 == 0) {
 #pragma unroll
-        for (int i = 0; i < EPT; ++i) acc_w[l - 1][i] = fmaf(hk, Rdz[l * HP + own_j0 + i], acc_w[l - 1][i]);
+          for (int i = 0; i < EPT; i += 4) {
+            const float4 d4 = *reinterpret_cast<const float4*>(dzl + i);
+            acc_w[l - 1][i] = fmaf(hk, d4.x, acc_w[l - 1][i]);
+            acc_w[l - 1][i + 1] = fmaf(hk, d4.y, acc_w[l - 1][i + 1]);
+            acc_w[l - 1][i + 2] = fmaf(hk, d4.z, acc_w[l - 1][i + 2]);
+            acc_w[l - 1][i + 3] = fmaf(hk, d4.w, acc_w[l - 1][i + 3]);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < EPT; ++i) acc_w[l - 1][i] = fmaf(hk, dzl[i], acc_w[l - 1][i]);
+        }
       }
+      {  // state rows of W0: entry e = tid + 512 i is (row e / HP, channel e % HP); 512 % HP == 0, so the channel -- and
+         // with it the dz operand -- is the same for all of a thread's entries
+        static_assert(PK_UPD_THREADS % HP == 0, "state-row ownership assumes HP divides the CTA size");
+        const float dzj = Rdz[tid % HP];
+        const int k0 = tid / HP;
 #pragma unroll
-      for (int i = 0; i < NS; ++i) {
-        const int e = tid + PK_UPD_THREADS * i;
-        if (e < PK_N_STATE * HP) acc_s[i] = fmaf(R[36 + e / HP], Rdz[e % HP], acc_s[i]);
+        for (int i = 0; i < NS; ++i) {
+          const int k = k0 + (PK_UPD_THREADS / HP) * i;
+          if (k < PK_N_STATE) acc_s[i] = fmaf(R[36 + k], dzj, acc_s[i]);
+        }
       }
     }
     // one-hot rows of W0: warp w owns rows with (row & 15) == w; pairs (t, slot) scanned 32 at a time
