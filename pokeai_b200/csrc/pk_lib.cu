@@ -52,6 +52,10 @@ struct PkGlobal {
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
+  // side stream of the wide backward: the HBM-bound column sums run beside the tensor-bound GEMMs (PK_WIDE_SIDE)
+  int wide_side = 1;
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 static PkGlobal g;
 
@@ -98,6 +102,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.pdl = env_int("PK_PDL", 1, 0, 1);
   g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 2);
   g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
+  g.wide_side = env_int("PK_WIDE_SIDE", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   return PK_OK;
 }
