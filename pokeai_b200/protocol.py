@@ -39,6 +39,38 @@ def _side_move_id(move_id: str) -> str:
     return move_id
 
 
+def get_possible_actions(battle_status, request: dict, tables: Optional[Tables] = None) -> list:
+    """The reference's function of the same name (common.py:143-174), for callers that want the PossibleAction list
+    itself (logging, `RLPolicyObservation`): same order, filtering and renames as `pack_actions_into` below.
+    `battle_status` is accepted and not read, as in the reference."""
+    from .observation import PossibleAction
+    tables = tables or load_tables()
+    force_switch = bool(request.get("forceSwitch"))
+    if not force_switch:
+        active = request["active"]
+        trapped = active[0].get("trapped")
+    else:
+        active, trapped = None, False
+    out = []
+    for poke_idx, member in enumerate(request["side"]["pokemon"]):
+        name = member["details"].split(",")[0]
+        poke_id = tables.species_ids[tables.species_name_to_idx[name]]  # dex.get_pokedex_by_name(name)['id']
+        all_moves = [_side_move_id(m) for m in member["moves"]]
+        if member["active"]:
+            if not force_switch:
+                for move_idx, move in enumerate(active[0]["moves"]):
+                    if not move.get("disabled"):
+                        out.append(PossibleAction(f"move {move_idx + 1}", poke_id,
+                                                  _active_move_id(move["id"], move["move"]), False, False, all_moves,
+                                                  member["item"]))
+        else:
+            if member["condition"].endswith(" fnt") or trapped:
+                continue
+            out.append(PossibleAction(f"switch {poke_idx + 1}", poke_id, None, True, force_switch, all_moves,
+                                      member["item"]))
+    return out
+
+
 def pack_actions_into(rec, request: dict, tables: Tables, max_actions: int = MAX_ACTIONS) -> List[str]:
     """Fill n_act / act[] of one record from a request; returns the simulator key of every slot.
     Order and filtering are get_possible_actions' (common.py:143-174): party order; the active member gives one

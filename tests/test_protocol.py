@@ -49,6 +49,14 @@ def test_pack_request_equals_possible_actions_route(cases, statuses, tables):
     assert recs[7].tobytes() == pack_request(*pairs[7], tables)[0].tobytes()
 
 
+def test_get_possible_actions_equals_reference(cases, tables):
+    """the restated get_possible_actions against the reference's outputs, field by field"""
+    from pokeai_b200.protocol import get_possible_actions
+    for i, c in enumerate(cases):
+        got = [pa._asdict() for pa in get_possible_actions(None, c["request"], tables)]
+        assert got == c["possible_actions"], i
+
+
 def test_pack_request_errors(cases, statuses, tables):
     from pokeai_b200.protocol import pack_request
     bs = statuses[0]
