@@ -157,8 +157,9 @@ def main():
     def step(i):
         s, s2, a, r, t = dev_sets[i % n_rot]
         if wide_net:  # tensor-core path: 2 next-state forwards, chosen-column forward + backward, clamp + Adam
-            loss = tr._wide_grad_device(s, s2, a, r, t, NG)
-            if world > 1:
+            overlap = world > 1 and args.allreduce != "nccl"  # per-layer buckets started from inside the backward
+            loss = tr._wide_grad_device(s, s2, a, r, t, NG, dist if overlap else None)
+            if world > 1 and not overlap:
                 dist.all_reduce(tr._grad, op=dist.ReduceOp.SUM)
             tr._wide_apply()
             return loss
@@ -241,7 +242,10 @@ def main():
                                     if px is not None else
                                     f"one NCCL sum-allreduce of {tr._flat.numel()} fp32 gradients per step, clamp + Adam "
                                     "after the reduce"),
-                       "exchange": "peer" if px is not None else ("nccl" if world > 1 else "none"),
+                       "exchange": "peer" if px is not None else
+                                   ("none" if world == 1 else
+                                    "nccl, one bucket per layer overlapped with the backward"
+                                    if wide_net and args.allreduce != "nccl" else "nccl"),
                        "l2": f"{n_rot} rotating transition sets; inputs are 297 B per transition (9.7 MB per set), "
                              "the kernels are compute/latency-bound, not HBM-bound"},
             "roofline": {"bound": "tensor (bf16 tcgen05 GEMMs)" if wide_net else

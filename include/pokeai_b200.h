@@ -307,6 +307,12 @@ PK_API int pk_wide_train_forward(const pk_obs* packed, int B, int A, const int32
                                  int n_layers, int n_channels, void* workspace, int32_t* mask, float* q, void* stream);
 PK_API int pk_wide_train_backward(const void* wide_prepared, int n_layers, int n_channels, int B, int A, int chosen_only,
                                   void* workspace, const float* dq, float* grad, void* stream);
+/* The same; layer_events: n_layers CUDA events (cudaEvent_t) or NULL.  layer_events[l] is recorded on `stream` once the
+ * gradient slices of layers >= l and of the head are complete: the caller can exchange them (NCCL, one bucket per
+ * layer, last layer first) while the backward of the earlier layers runs. */
+PK_API int pk_wide_train_backward_ev(const void* wprep, int n_layers, int n_channels, int B, int A, int chosen_only,
+                              void* workspace, const float* dq, float* grad, void* const* layer_events,
+                              void* stream);
 /* Double-DQN target y = r + gamma * Q_target(s', argmax_legal Q_online(s')) (0 for terminal), Huber loss (mean over
  * n_global) and dq = clamp(q_sa - y, -1, 1) / n_global: trainer.py:163-187 for the wide path.  Fixed-order sums. */
 PK_API int pk_wide_dqn_dq(const float* q_sa, const float* q_next_online, const float* q_next_target,

@@ -72,6 +72,7 @@ _SIGNATURES = {
     "pk_wide_train_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "pk_wide_train_forward": (C.c_int, [_vp, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "pk_wide_train_backward": (C.c_int, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "pk_wide_train_backward_ev": (C.c_int, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "pk_wide_dqn_dq": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _vp]),
     "pk_wide_prepared_bytes": (_sz, [_i, _i, _i]),
     "pk_wide_prepare": (C.c_int, [C.POINTER(pk_mlp), _vp, _vp]),

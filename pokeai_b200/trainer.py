@@ -359,8 +359,11 @@ class Trainer:
             self._px = PeerGradExchange.create(self._flat.numel(), self.device)
         return self._px
 
-    def _wide_grad_device(self, s_d, s2_d, a_d, r_d, t_d, n_global: int):
-        """Device-resident part of the wide update: fills self._grad, returns the loss tensor (1,)."""
+    def _wide_grad_device(self, s_d, s2_d, a_d, r_d, t_d, n_global: int, dist=None):
+        """Device-resident part of the wide update: fills self._grad, returns the loss tensor (1,).
+        With `dist` (an active NCCL group) the gradient is also summed over ranks, one bucket per layer, each started as
+        soon as that layer's slice is complete, so the 55 MB exchange overlaps the backward of the earlier layers
+        (SURVEY.md 8e); the caller must not all-reduce self._grad again."""
         from . import wide
         n, A = s_d.shape[0], self.feature_extractor.output_dim
         if getattr(self, "_wide_ws", None) is None or self._wide_ws_n < n:
@@ -373,7 +376,25 @@ class Trainer:
         _, q_sa = wide.train_forward(s_d, A, self._prepared, self._nl, self._H, ws, col_select=a_d)
         dq, loss = wide.dqn_dq(q_sa, q_no if self.double_dqn else None, q_nt, m2, r_d, t_d, n_global, self.gamma,
                                self.double_dqn)
-        wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True)
+        if dist is None:
+            wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True)
+            return loss
+        if getattr(self, "_wide_events", None) is None:
+            self._wide_events = [torch.cuda.Event() for _ in range(self._nl)]
+            for e in self._wide_events:
+                e.record()  # materialises the CUDA event so that the library can record it
+            self._wide_comm = torch.cuda.Stream(self.device)
+            self._wide_buckets = wide.layer_grad_buckets(self._nl, self._H)
+        main = torch.cuda.current_stream(self.device)
+        wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True,
+                            layer_events=self._wide_events)
+        comm = self._wide_comm
+        with torch.cuda.stream(comm):
+            for l in range(self._nl - 1, -1, -1):  # the order the backward finishes them in
+                comm.wait_event(self._wide_events[l])
+                lo, hi = self._wide_buckets[l]
+                dist.all_reduce(self._grad[lo:hi], op=dist.ReduceOp.SUM)
+        main.wait_stream(comm)
         return loss
 
     def _wide_apply(self) -> None:
@@ -403,12 +424,22 @@ class Trainer:
             a_d = torch.from_numpy(np.ascontiguousarray(action, dtype=np.int32)).to(dev)
             r_d = torch.from_numpy(np.ascontiguousarray(reward, dtype=np.float32)).to(dev)
             t_d = torch.from_numpy(np.ascontiguousarray(terminal, dtype=np.uint8)).to(dev)
-            loss = self._wide_grad_device(s_d, s2_d, a_d, r_d, t_d, n_global)
-            self._loss.copy_(loss)
         dist = self._dist()
+        nccl = dist is not None and dist.get_backend() == "nccl"
+        if n > 0:
+            # NCCL group: the gradient is reduced bucket by bucket inside, overlapped with the backward
+            loss = self._wide_grad_device(s_d, s2_d, a_d, r_d, t_d, n_global, dist if nccl else None)
+            self._loss.copy_(loss)
         if dist is not None:
-            from .dist import allreduce_sum_
-            allreduce_sum_(self._grad, self._loss, dist)
+            if nccl:
+                if n == 0:  # an empty shard still takes part in the same per-layer collectives, in the same order
+                    from . import wide as _w
+                    for lo, hi in reversed(_w.layer_grad_buckets(self._nl, self._H)):
+                        dist.all_reduce(self._grad[lo:hi], op=dist.ReduceOp.SUM)
+                dist.all_reduce(self._loss, op=dist.ReduceOp.SUM)
+            else:
+                from .dist import allreduce_sum_
+                allreduce_sum_(self._grad, self._loss, dist)
         self._wide_apply()
         return float(self._loss.item())
 

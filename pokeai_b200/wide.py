@@ -185,15 +185,36 @@ def train_forward(packed: torch.Tensor, A: int, prepared: torch.Tensor, n_layers
 
 
 def train_backward(prepared: torch.Tensor, n_layers: int, H: int, B: int, A: int, ws: torch.Tensor, dq: torch.Tensor,
-                   out_grad: Optional[torch.Tensor] = None, chosen_only: bool = False) -> torch.Tensor:
-    """dq = d loss / d q ((B, A), or (B,) after a col_select forward) -> flat fp32 gradient in state_dict order."""
+                   out_grad: Optional[torch.Tensor] = None, chosen_only: bool = False,
+                   layer_events: Optional[list] = None) -> torch.Tensor:
+    """dq = d loss / d q ((B, A), or (B,) after a col_select forward) -> flat fp32 gradient in state_dict order.
+    layer_events: n_layers torch.cuda.Event objects (each recorded at least once before); event l is recorded when the
+    gradient of layers >= l and of the head is complete (see `layer_grad_buckets`)."""
     dev = _dev(dq)
     assert dq.dtype == torch.float32 and dq.is_contiguous() and dq.numel() == (B if chosen_only else B * A)
     n = N.lib().pk_mlp_param_floats(n_layers, H, n_channels())
     grad = out_grad if out_grad is not None else torch.empty(n, dtype=torch.float32, device=dev)
-    N.check(N.lib().pk_wide_train_backward(prepared.data_ptr(), n_layers, H, B, A, 1 if chosen_only else 0,
-                                           ws.data_ptr(), dq.data_ptr(), grad.data_ptr(), _stream_ptr(dev)))
+    evp = None
+    if layer_events is not None:
+        assert len(layer_events) == n_layers
+        evp = (C.c_void_p * n_layers)(*[int(e.cuda_event) for e in layer_events])
+        assert all(evp[i] for i in range(n_layers)), "record every layer event once before the first use"
+    N.check(N.lib().pk_wide_train_backward_ev(prepared.data_ptr(), n_layers, H, B, A, 1 if chosen_only else 0,
+                                              ws.data_ptr(), dq.data_ptr(), grad.data_ptr(), evp, _stream_ptr(dev)))
     return grad
+
+
+def layer_grad_buckets(n_layers: int, H: int) -> list:
+    """[(lo, hi)] per layer: the contiguous slice of the flat gradient that is complete when layer event l fires and
+    was not complete before (layer l's weight + bias; the last layer's bucket also holds the head)."""
+    Cn = n_channels()
+    out, off = [], 0
+    for l in range(n_layers):
+        size = H * (Cn if l == 0 else H) + H
+        out.append([off, off + size])
+        off += size
+    out[-1][1] = off + H + 1
+    return [tuple(b) for b in out]
 
 
 def dqn_dq(q_sa, q_next_online, q_next_target, mask_next, reward, terminal, n_global: int, gamma: float,
