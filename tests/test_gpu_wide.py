@@ -281,3 +281,18 @@ def test_wide_trainer_update_matches_oracle(tables, dev):
     with torch.no_grad():
         q_ref = ref_port.mlp_forward(sd1, torch.from_numpy(f[:8])).numpy()
     np.testing.assert_allclose(q_new, q_ref, rtol=0, atol=2e-2)
+
+
+def test_wide_overlapped_exchange_two_gpus():
+    """per-layer NCCL buckets started from inside the backward (pk_wide_train_backward_ev) against one allreduce after
+    it, one process per GPU: tools/check_wide_overlap.py under torchrun.  Needs two GPUs; skipped on a one-GPU box."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = Path(__file__).resolve().parents[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29583", str(root / "tools" / "check_wide_overlap.py")],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "wide overlap ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
