@@ -153,6 +153,15 @@ PK_API int pk_set_overlap_launches(int on);
  * materialised (the measured optimum, profiles/r01_pair_vs_single.txt).  Results are identical up to fp32
  * summation order. */
 PK_API int pk_debug_set_pairing(int mode);
+/* Tuning / test aid: pk_decide for 64-channel networks with one or two hidden layers (the default MLP 2 x 64) has a
+ * second kernel (pk_decide_tc.cuh) in which the hidden layers of the eight battles of a warp group run as ONE
+ * tcgen05.mma.kind::tf32 contraction with a 3-term hi/lo split (fp32-accurate: Q stays within the 1e-5 tolerance),
+ * accumulators in TMEM, operand tiles staged by TMA from the prepared weights.  0 (default) = never, 1 = when features
+ * are materialised, 2 = always; PK_DECIDE_TC in the environment.  Same results up to fp32 summation order, covered by
+ * the same parity tests.  Measured on B200: 28.0 us against 22.9 us per 4 096-state launch -- 24
+ * dependent K = 8 MMAs per layer are latency-bound at this size and the shared memory they need takes the L1 the
+ * layer-0 gathers live in -- so it is off by default. */
+PK_API int pk_debug_set_decide_tc(int mode);
 /* Tuning / test aid: 1 runs the 64-channel hidden layers of pk_decide's one-battle-per-warp kernel on the warp-level
  * tensor path (mma.sync tf32 with a 3-term hi/lo split: fp32-accurate, Q stays within the 1e-5 tolerance); 0 (default)
  * keeps them on the FP32 pipe (FFMA2).  Measured on B200 (profiles/r01_hidden_tc.txt): the legacy mma.sync path is no

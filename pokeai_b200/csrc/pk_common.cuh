@@ -54,13 +54,31 @@ struct PkDeviceTables {
 //   wout [HP], bout [4]                                   <- `total` ends here (what inference reads)
 //   wn[l] [HP][HP] (l = 1..n_layers-1): the same hidden matrices NOT transposed, row j = output channel,
 //                  read by the backward pass (dh = W^T dz)           <- `total_train` ends here
+//   tc[l] (HP == 64 only, l = 1..n_layers-1): the same hidden matrix as the B operand of tcgen05.mma.kind::tf32 --
+//                  two 64 x 64 fp32 tiles, hi = tf32(w) and lo = w - hi, each in the K-major SWIZZLE_128B shared-memory
+//                  layout (pk_tc_tile_off), so pk_decide_tc_kernel stages them with one TMA bulk load   <- `total_all`
+#define PK_TC_TILE_FLOATS 4096u
 struct PkLayout {
   int C, H, HP, n_layers;
-  unsigned w1t, wout, bout, total, total_train;
+  unsigned w1t, wout, bout, total, total_train, total_all;
   unsigned b[PK_MAX_LAYERS];
   unsigned wl[PK_MAX_LAYERS];
   unsigned wn[PK_MAX_LAYERS];
+  unsigned tc[PK_MAX_LAYERS];
 };
+
+// float offset of element (row, k) of a K-major SWIZZLE_128B fp32 operand tile with 64 rows x 64 k: k-blocks of 32
+// floats (128 B) are whole sub-tiles of `kb_floats`; inside one, 8-row groups are 1024 B apart and the 16-byte chunk
+// index is XORed with the row's index in its group (cute Swizzle<3,4,3>)
+__host__ __device__ inline unsigned pk_tc_tile_off(unsigned row, unsigned k, unsigned kb_floats) {
+  const unsigned kb = k >> 5, chunk = (k >> 2) & 7u, r8 = row & 7u;
+  return kb * kb_floats + (row >> 3) * 256u + r8 * 32u + ((chunk ^ r8) << 2) + (k & 3u);
+}
+__device__ __forceinline__ float pk_tf32_hi(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
 
 __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
   PkLayout L;
@@ -99,6 +117,15 @@ __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
     }
   }
   L.total_train = o;
+  for (int l = 0; l < PK_MAX_LAYERS; ++l) {
+    if (l >= 1 && l < n_layers && L.HP == 64) {
+      L.tc[l] = o;
+      o += 2u * PK_TC_TILE_FLOATS;
+    } else {
+      L.tc[l] = 0;
+    }
+  }
+  L.total_all = o;
   return L;
 }
 
@@ -106,7 +133,7 @@ __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
 // untransposed copy for hidden-layer weights, 0 otherwise
 struct PkParamLayout;
 __host__ __device__ inline unsigned pk_flat_to_prepared(const PkParamLayout& P, const PkLayout& L, unsigned i,
-                                                        unsigned* wn_off);
+                                                        unsigned* wn_off, unsigned* tc_off = nullptr);
 
 // Flat parameter vector in state_dict order (layers.i.weight, layers.i.bias, ..., output.weight, output.bias)
 struct PkParamLayout {
@@ -139,14 +166,18 @@ __host__ __device__ inline PkParamLayout pk_make_param_layout(int n_layers, int 
   return P;
 }
 
+// *tc_off (optional) = offset of the hi element in the tensor-core tile of a hidden-layer weight (lo at
+// + PK_TC_TILE_FLOATS), 0 when the layout has none
 __host__ __device__ inline unsigned pk_flat_to_prepared(const PkParamLayout& P, const PkLayout& L, unsigned i,
-                                                        unsigned* wn_off) {
+                                                        unsigned* wn_off, unsigned* tc_off) {
   *wn_off = 0;
+  if (tc_off) *tc_off = 0;
   for (int l = 0; l < P.n_layers; ++l) {
     if (i < P.b[l]) {
       const unsigned e = i - P.w[l], cin = l == 0 ? (unsigned)P.C : (unsigned)P.H;
       const unsigned j = e / cin, k = e - j * cin;
       if (l > 0) *wn_off = L.wn[l] + j * L.HP + k;
+      if (l > 0 && tc_off && L.tc[l]) *tc_off = L.tc[l] + pk_tc_tile_off(j, k, 2048u);
       return (l == 0 ? L.w1t : L.wl[l]) + k * L.HP + j;
     }
     if (i < P.b[l] + (unsigned)P.H) return L.b[l] + (i - P.b[l]);

@@ -480,7 +480,7 @@ __device__ __forceinline__ void pk_stage_weights(unsigned char* smem, const PkSm
 // (pk_poke_feature_block), for the TMA variant only after cp.async.bulk.wait_group has returned.
 template <int A>
 __device__ __forceinline__ void pk_store_feature_block(float* __restrict__ g, int L, const float* sv,
-                                                       const float* zero_tile, int lane) {
+                                                       const float* zero_tile, int lane, uint32_t zero_tile_bytes = 0) {
   const int m = (int)((reinterpret_cast<uintptr_t>(g) >> 2) & 3u);  // phase of the block inside a 16 B line
   const int hc = (4 - m) & 3;                                       // floats before the first 16 B boundary
   const int nchunks = (L - hc) >> 2;                                // whole 16 B chunks
@@ -489,7 +489,18 @@ __device__ __forceinline__ void pk_store_feature_block(float* __restrict__ g, in
   // chunks that overlap the state region carry values; everything behind is zeros until poked
   const int n_state_chunks = min(nchunks, (ns - hc + 3) >> 2);
   if (zero_tile != nullptr && lane == 0 && nchunks > n_state_chunks) {
-    pk_bulk_store(g4 + n_state_chunks, zero_tile, (uint32_t)(nchunks - n_state_chunks) * 16u);
+    uint32_t left = (uint32_t)(nchunks - n_state_chunks) * 16u;
+    if (zero_tile_bytes == 0 || zero_tile_bytes >= left) {
+      pk_bulk_store(g4 + n_state_chunks, zero_tile, left);
+    } else {  // a tile smaller than the zero run: several bulk stores from the same tile, one group
+      unsigned char* dst = reinterpret_cast<unsigned char*>(g4 + n_state_chunks);
+      while (left != 0) {
+        const uint32_t n = left < zero_tile_bytes ? left : zero_tile_bytes;
+        pk_bulk_store(dst, zero_tile, n);
+        dst += n;
+        left -= n;
+      }
+    }
     pk_bulk_commit();
   }
   for (int j = lane; j < n_state_chunks; j += 32) {
@@ -611,21 +622,27 @@ pk_decide_kernel(const uint4* __restrict__ packed, int B, const float* __restric
   pk_trace(tr, tslot, 1);
   if (b < B) take_and_parse();
   pk_trace(tr, tslot, 2);
-  if (with_mlp || use_tma) __syncthreads();
   // Programmatic dependent launch: everything above reads only the packed records and fills shared memory, so it
   // may run while the previous launch of this stream is still finishing.  Weights (which a preceding pk_clamp_adam may
-  // have written) are read and every global WRITE happens below this wait, which returns once the preceding kernel
-  // has completed and flushed.  Both griddepcontrol instructions are no-ops for a normal launch.
-  pk_grid_dependency_wait();
-  // the network's small tensors (biases, hidden matrices, head; the 50 state rows of W0^T: 30 KB for 2 x 64) are
-  // staged by two TMA bulk loads issued by one thread; they land while the first battle's features are stored, and
-  // the mbarrier is waited for just before the first use of the weights
-  if (with_mlp && threadIdx.x == 0) {
-    const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
-    pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
-    pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
-    pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
+  // have written) are read and every global WRITE happens below griddepcontrol.wait, which returns once the preceding
+  // kernel has completed and flushed.  Both griddepcontrol instructions are no-ops for a normal launch.
+  // The network's small tensors (biases, hidden matrices, head; the 50 state rows of W0^T: 30 KB for 2 x 64) are staged
+  // by two TMA bulk loads issued by one thread BEFORE the prologue barrier, i.e. before any warp's feature fill: the
+  // SM's TMA unit serves requests in order, and loads queued behind sixteen 20 KB fills land microseconds later
+  // (measured on the tensor-core variant).  They land while the first battle's features are stored;
+  // the mbarrier is waited for just before the first use of the weights.
+  if (with_mlp && warp == 0) {
+    pk_grid_dependency_wait();
+    if (lane == 0) {
+      const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
+      pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
+      pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
+      pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
+    }
+    __syncwarp();
   }
+  if (with_mlp || use_tma) __syncthreads();
+  pk_grid_dependency_wait();
   if constexpr (TC) {
     if (with_mlp) {
       for (int l = 1; l < lay.n_layers; ++l)
@@ -1044,4 +1061,16 @@ __global__ void pk_pad2d_kernel(const float* __restrict__ src, float* __restrict
 __global__ void pk_copy_pad_kernel(const float* __restrict__ src, float* __restrict__ dst, int n, int n_pad) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_pad) dst[i] = i < n ? src[i] : 0.0f;
+}
+// src (rows, cols) row-major hidden matrix -> tensor-core operand tiles (PkLayout::tc): hi tile then lo tile,
+// 64 x 64 each, zero padded, K-major SWIZZLE_128B order
+__global__ void pk_tc_tiles_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int cols) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * 64) return;
+  const int j = i >> 6, k = i & 63;
+  const float w = (j < rows && k < cols) ? src[(size_t)j * cols + k] : 0.0f;
+  const float hi = pk_tf32_hi(w);
+  const unsigned off = pk_tc_tile_off((unsigned)j, (unsigned)k, 2048u);
+  dst[off] = hi;
+  dst[off + PK_TC_TILE_FLOATS] = w - hi;
 }

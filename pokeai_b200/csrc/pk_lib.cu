@@ -12,6 +12,7 @@
 #include "pk_decide2.cuh"
 #include "pk_update.cuh"
 #include "pk_wide.cuh"
+#include "pk_decide_tc.cuh"
 
 // ---- error handling -----------------------------------------------------------------------------
 static thread_local char g_err[512] = "";
@@ -45,6 +46,7 @@ struct PkGlobal {
   int decide_warps = 16;
   int encode_warps = 16;
   int decide_pair = 1;
+  int decide_tc = 0;  // 64-channel nets: hidden layers on tcgen05 (PK_DECIDE_TC: 0 never (measured best), 1 when features are written, 2 always)
   int hidden_tc = 0;
   int pdl = 1;        // pk_decide launches carry the programmatic-stream-serialization attribute (PK_PDL)
   int dense_warps = 16;  // warps per CTA of the dense-input forward (PK_DENSE_WARPS; kernel iteration only)
@@ -104,6 +106,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
   g.wide_side = env_int("PK_WIDE_SIDE", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
+  g.decide_tc = env_int("PK_DECIDE_TC", 0, 0, 2);
   return PK_OK;
 }
 
@@ -124,6 +127,11 @@ extern "C" int pk_debug_set_hidden_tc(int on) {
   g.hidden_tc = on ? 1 : 0;
   return PK_OK;
 }
+extern "C" int pk_debug_set_decide_tc(int mode) {
+  if (mode < 0 || mode > 2) return pk_fail(PK_ERR_INVALID, "pk_debug_set_decide_tc: mode %d not in 0..2", mode);
+  g.decide_tc = mode;
+  return PK_OK;
+}
 extern "C" int pk_debug_set_pairing(int mode) {
   if (mode < 0 || mode > 2) return pk_fail(PK_ERR_INVALID, "pk_debug_set_pairing: mode %d not in 0..2", mode);
   g.decide_pair = mode;
@@ -135,7 +143,7 @@ extern "C" int pk_sm_count(void) { return g.device < 0 ? 0 : g.sm_count; }
 // ---- weights --------------------------------------------------------------------------------------
 extern "C" size_t pk_mlp_prepared_floats(int n_layers, int n_channels, int in_channels) {
   if (n_layers < 1 || n_layers > PK_MAX_LAYERS || n_channels < 1 || in_channels < 1) return 0;
-  return pk_make_layout(n_layers, n_channels, in_channels).total_train;
+  return pk_make_layout(n_layers, n_channels, in_channels).total_all;
 }
 extern "C" size_t pk_mlp_param_floats(int n_layers, int n_channels, int in_channels) {
   if (n_layers < 1 || n_layers > PK_MAX_LAYERS || n_channels < 1 || in_channels < 1) return 0;
@@ -155,6 +163,8 @@ static int pk_prepare_impl(const pk_mlp* m, float* prepared, cudaStream_t st) {
     pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->b[l], prepared + lay.b[l], H, HP);
     if (l > 0)  // untransposed padded copy for the backward pass
       pk_pad2d_kernel<<<(unsigned)(((long long)HP * HP + T - 1) / T), T, 0, st>>>(m->w[l], prepared + lay.wn[l], H, H, HP);
+    if (l > 0 && lay.tc[l])  // tcgen05 operand tiles (hi / lo, swizzled) for pk_decide_tc_kernel
+      pk_tc_tiles_kernel<<<(64 * 64 + T - 1) / T, T, 0, st>>>(m->w[l], prepared + lay.tc[l], H, H);
   }
   PK_REQUIRE(m->w_out != nullptr && m->b_out != nullptr, "pk_mlp_prepare: null output tensor");
   pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->w_out, prepared + lay.wout, H, HP);
@@ -256,6 +266,36 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   const int CPL = lay.HP / 32;
   const bool use_tma = feat != nullptr && g.zero_by_tma != 0;
   const uint4* pk = reinterpret_cast<const uint4*>(packed);
+  // 64-channel networks with one or two hidden layers: the hidden layers of the four battles of a warp group run as
+  // one tcgen05 contraction (pk_decide_tc.cuh)
+  if (with_mlp && lay.HP == 64 && n_layers >= 2 && (g.decide_tc == 2 || (g.decide_tc == 1 && feat != nullptr))) {
+    const PktSmemPlan tplan = pkt_smem_plan(lay, A, use_tma, (unsigned)g.max_smem);
+    if (tplan.total <= (unsigned)g.max_smem) {
+      int tgrid = (B + PKT_WARPS - 1) / PKT_WARPS;
+      if (tgrid > g.sm_count) tgrid = g.sm_count;
+#define PK_LAUNCH_TC(A_)                                                                                          \
+  {                                                                                                               \
+    int rc_ = pk_set_smem(pk_decide_tc_kernel<A_>, tplan.total);                                                  \
+    if (rc_) return rc_;                                                                                          \
+    PK_CUDA(pk_launch_pdl(pk_decide_tc_kernel<A_>, tgrid, PKT_WARPS * 32, tplan.total, st, g.pdl != 0, pk, B,     \
+                          prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0, (unsigned)g.max_smem));      \
+  }
+      switch (A) {
+        case 1: PK_LAUNCH_TC(1) break;
+        case 2: PK_LAUNCH_TC(2) break;
+        case 3: PK_LAUNCH_TC(3) break;
+        case 4: PK_LAUNCH_TC(4) break;
+        case 5: PK_LAUNCH_TC(5) break;
+        case 6: PK_LAUNCH_TC(6) break;
+        case 7: PK_LAUNCH_TC(7) break;
+        case 8: PK_LAUNCH_TC(8) break;
+        default: PK_LAUNCH_TC(9) break;
+      }
+#undef PK_LAUNCH_TC
+      PK_CUDA(cudaGetLastError());
+      return PK_OK;
+    }
+  }
   // measured (profiles/r01_pair_vs_single.txt): pairing wins when the features are not materialised (305 vs 275 M
   // decisions/s at 65 536 states) and loses when they are (two 22 KB blocks per warp back-pressure the store path)
   if (with_mlp && lay.HP <= 64 && (g.decide_pair == 2 || (g.decide_pair == 1 && feat == nullptr))) {
@@ -496,7 +536,7 @@ extern "C" int pk_session_load_weights(pk_session* s, const pk_mlp* hm) {
   s->d_params = s->d_prepared = nullptr;
   s->prepared = nullptr;
   PK_CUDA(cudaMalloc(&s->d_params, (size_t)P.total * sizeof(float)));
-  PK_CUDA(cudaMalloc(&s->d_prepared, (size_t)lay.total_train * sizeof(float)));
+  PK_CUDA(cudaMalloc(&s->d_prepared, (size_t)lay.total_all * sizeof(float)));
   pk_mlp dm = *hm;
   const int H = hm->n_channels;
   for (int l = 0; l < hm->n_layers; ++l) {

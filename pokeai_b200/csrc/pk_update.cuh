@@ -435,9 +435,14 @@ __global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe
   v[i] = vi;
   params[i] = p;
   if (prepared != nullptr) {
-    unsigned wn;
-    prepared[pk_flat_to_prepared(P, lay, i, &wn)] = p;
+    unsigned wn, tc;
+    prepared[pk_flat_to_prepared(P, lay, i, &wn, &tc)] = p;
     if (wn) prepared[wn] = p;
+    if (tc) {  // tensor-core operand tiles of pk_decide_tc_kernel: hi = tf32(p), lo = p - hi
+      const float hi = pk_tf32_hi(p);
+      prepared[tc] = hi;
+      prepared[tc + PK_TC_TILE_FLOATS] = p - hi;
+    }
   }
 }
 
@@ -455,8 +460,13 @@ __global__ void pk_clamp_adam_kernel(float* __restrict__ params, const float* __
   v[i] = vi;
   params[i] = p;
   if (prepared != nullptr) {
-    unsigned wn;
-    prepared[pk_flat_to_prepared(P, lay, i, &wn)] = p;
+    unsigned wn, tc;
+    prepared[pk_flat_to_prepared(P, lay, i, &wn, &tc)] = p;
     if (wn) prepared[wn] = p;
+    if (tc) {  // tensor-core operand tiles of pk_decide_tc_kernel: hi = tf32(p), lo = p - hi
+      const float hi = pk_tf32_hi(p);
+      prepared[tc] = hi;
+      prepared[tc + PK_TC_TILE_FLOATS] = p - hi;
+    }
   }
 }

@@ -228,6 +228,7 @@ def test_paired_and_single_kernels_agree_with_oracle(tables, dev, ps, nl, H, B):
         qo = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
     prepared, _, _, _ = ops.prepare_weights(sd, dev)
     try:
+        N.check(N.lib().pk_debug_set_decide_tc(0))
         for mode in (0, 2):
             N.check(N.lib().pk_debug_set_pairing(mode))
             for mat in (True, False):
@@ -240,6 +241,46 @@ def test_paired_and_single_kernels_agree_with_oracle(tables, dev, ps, nl, H, B):
                     assert np.array_equal(bits(f.cpu().numpy()), bits(fo)), f"pairing={mode}"
     finally:
         N.check(N.lib().pk_debug_set_pairing(1))
+        N.check(N.lib().pk_debug_set_decide_tc(1))
+
+
+@pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 64, 4096), (6, 2, 64, 4097), (6, 2, 64, 1), (6, 2, 64, 13), (6, 3, 64, 700),
+                                       (3, 2, 48, 301), (1, 4, 64, 65), (4, 2, 33, 100), (2, 3, 64, 2500),
+                                       (6, 2, 64, 30011)])
+def test_tcgen05_hidden_layers_match_fp32_oracle(tables, dev, ps, nl, H, B):
+    """pk_decide_tc_kernel: the hidden layers of the eight battles of a warp group as one tcgen05.mma.kind::tf32
+    contraction (3-term hi/lo split, TMEM accumulator; PK_DECIDE_TC, off by default).  Same bar as the FP32-pipe kernels: features / masks bit-exact, Q within
+    1e-5, the action the exact masked argmax of the kernel's own Q; and the two paths agree closely.  Batch sizes
+    cover a partly filled last round, a single battle, and more rounds than two."""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200 import _native as N, ops
+    from pokeai_b200.packed import synth_packed
+    A = 4 + ps - 1
+    rec = synth_packed(B, seed=13 * B + H, party_size=ps, kind="ragged", tables=tables)
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=H + 5 * nl)
+    fo, mo = packed_oracle.encode(rec, ps, tables)
+    with torch.no_grad():
+        qo = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+    prepared, _, _, _ = ops.prepare_weights(sd, dev)
+    qs = {}
+    try:
+        for mode in (2, 0):
+            N.check(N.lib().pk_debug_set_decide_tc(mode))
+            for mat in (True, False):
+                f, m, q, a = ops.decide(_to_dev(rec, dev), A, prepared, nl, H, materialise=mat)
+                qg = q.cpu().numpy()
+                np.testing.assert_allclose(qg, qo, rtol=Q_RTOL, atol=Q_ATOL, err_msg=f"decide_tc={mode} mat={mat}")
+                assert np.array_equal(m.cpu().numpy(), mo)
+                assert np.array_equal(a.cpu().numpy(), ref_port.masked_argmax(qg, mo))
+                if mat:
+                    assert np.array_equal(bits(f.cpu().numpy()), bits(fo)), f"decide_tc={mode}"
+                qs[(mode, mat)] = qg
+    finally:
+        N.check(N.lib().pk_debug_set_decide_tc(1))
+    assert np.abs(qs[(2, True)] - qs[(0, True)]).max() < 5e-6
+    assert np.abs(qs[(2, True)] - qs[(2, False)]).max() < 5e-6
+    if nl <= 3 and 32 < H <= 64:  # the tensor-core kernel really ran (deeper nets fall back: shared memory)
+        assert np.array_equal(qs[(2, True)], qs[(2, False)])  # same kernel with and without the feature stores
 
 
 @pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 64, 4096), (6, 3, 64, 513), (3, 2, 48, 200), (1, 4, 64, 65), (6, 2, 33, 100)])
@@ -259,6 +300,7 @@ def test_tensor_path_hidden_layer_matches_fp32_oracle(tables, dev, ps, nl, H, B)
     qs = {}
     try:
         N.check(N.lib().pk_debug_set_pairing(0))
+        N.check(N.lib().pk_debug_set_decide_tc(0))
         for on in (1, 0):
             N.check(N.lib().pk_debug_set_hidden_tc(on))
             for mat in (True, False):
@@ -273,6 +315,7 @@ def test_tensor_path_hidden_layer_matches_fp32_oracle(tables, dev, ps, nl, H, B)
     finally:
         N.check(N.lib().pk_debug_set_hidden_tc(0))
         N.check(N.lib().pk_debug_set_pairing(1))
+        N.check(N.lib().pk_debug_set_decide_tc(1))
     assert np.abs(qs[(1, True)] - qs[(0, True)]).max() < 5e-6
 
 
