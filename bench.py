@@ -333,6 +333,11 @@ def b200_arm(args, rank, local_rank, world):
     qs = [torch.empty((B, A), dtype=torch.float32, device=dev) for _ in range(n_rot)]
     acts = [torch.empty((B,), dtype=torch.int32, device=dev) for _ in range(n_rot)]
 
+    # programmatic dependent launch is opt-in for the device-pointer API (include/pokeai_b200.h): the records of every
+    # launch were uploaded above, none is produced by a preceding kernel, so the contract holds
+    from pokeai_b200 import _native as N
+    N.check(N.lib().pk_set_overlap_launches(1))
+
     def step(i):
         j = i % n_rot
         ops.decide(pk[j], A, prepared, nl, H, out_feat=feats[j], out_mask=masks[j], out_q=qs[j], out_action=acts[j])
@@ -494,8 +499,8 @@ def b200_arm(args, rank, local_rank, world):
                          "pk_decide_kernel",
                          "algorithmic_bytes_per_launch": ALG_BYTES_PER_DECISION * B, "peak_source": peak_src,
                          "launch_us": launch_ms * 1e3, "launches_timed": n_launch,
-                         "overlap": "programmatic dependent launch: the record-only prologue of launch i+1 overlaps the "
-                                    "tail of launch i (PK_PDL)",
+                         "overlap": "programmatic dependent launch, opted into with pk_set_overlap_launches(1): the "
+                                    "record-only prologue of launch i+1 overlaps the tail of launch i",
                          "launch": (f"one CUDA-graph replay of {G} launches per step" if graph is not None
                                     else f"{G} Python-issued launches per step"),
                          "l2": f"{n_rot} rotating input/output sets ({n_rot * feat_bytes / 1e6:.0f} MB of outputs) "

@@ -141,12 +141,15 @@ PK_API int pk_n_channels(void);
 /* Debugging aid: when non-NULL, pk_encode / pk_decide record %globaltimer (ns) of lane 0 at 10 phase points of
  * the first battle of every warp into device_buffer[(cta * warps + warp) * 16 + phase].  NULL switches it off. */
 PK_API int pk_debug_set_trace(unsigned long long* device_buffer);
-/* pk_decide / pk_encode launches carry the programmatic-dependent-launch attribute (default on; PK_PDL=0 or
- * pk_set_overlap_launches(0) turns it off): the part of the kernel that only reads the PACKED RECORDS and fills shared
- * memory may overlap the tail of the previous kernel of the stream; weights are read and all outputs are written after
- * griddepcontrol.wait, i.e. after that kernel has completed.  Contract: the packed records must not be produced by the
- * kernel launched immediately before on the same stream (records that arrive by cudaMemcpy, or that were written
- * earlier, are fine -- every caller in this repository satisfies this).  Worth 2 us per 4 096-state launch. */
+/* Programmatic dependent launch for the device-pointer entry points pk_decide / pk_encode: OFF by default, opt-in per
+ * process with pk_set_overlap_launches(1) (or PK_PDL=1).  When on, the part of the kernel that only reads the PACKED
+ * RECORDS and fills shared memory may overlap the tail of the previous kernel of the stream; weights are read and all
+ * outputs are written after griddepcontrol.wait, i.e. after that kernel has completed.  The caller who opts in asserts
+ * that the packed records are NOT produced by the kernel launched immediately before on the same stream (records that
+ * arrive by cudaMemcpy, or that were written earlier, are fine).  Worth 2 us per 4 096-state launch; bench.py opts in
+ * (its records are uploaded once, before the timed region).  The host-buffer sessions (pk_session_*), whose records
+ * always come from host memory, use it on their own (PK_PDL_SESSION=0 turns that off); the update's next-state
+ * forwards never do. */
 PK_API int pk_set_overlap_launches(int on);
 /* Tuning / test aid: which pk_decide kernel runs for networks of <= 64 channels.  0 = one battle per warp,
  * 2 = two battles per warp (one per half-warp in the MLP), 1 (default) = paired only when features are not
@@ -240,7 +243,10 @@ PK_API int pk_clamp_adam(float* params, const float* grad, float* exp_avg, float
  * epoch: 1, 2, 3, ... the same on every rank; buffers must alternate between two sets by epoch parity (a rank may
  * overwrite the set of epoch e only after its own call for epoch e + 1).  Every rank of the job must make the call.
  * grad_sum (n_params floats, may be NULL) receives the reduced pre-clamp gradient; loss_status (2 floats, may be
- * NULL): [0] = sum of the loss shares, [1] = 1.0 if a peer did not arrive within ~2 s (the step is then invalid).
+ * NULL): [0] = sum of the loss shares, [1] = 1.0 if a peer did not arrive within the time limit (30 s;
+ * PK_PEER_TIMEOUT_MS in the environment).  A thread block that gives up returns WITHOUT writing params, exp_avg,
+ * exp_avg_sq or prepared, so a timed-out step leaves the state as it was (block-granular: the blocks of one launch
+ * start within microseconds of each other and wait for the same flags); the caller must treat the step as not taken.
  * The sum runs in rank order on every rank: identical bits everywhere. */
 #define PK_MAX_PEERS 8
 PK_API int pk_peer_clamp_adam(float* params, const float* const* peer_grads, uint32_t* const* peer_flags, int rank,

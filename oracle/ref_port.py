@@ -10,7 +10,8 @@ log fixture and on seeded synthetic observations and commits its outputs under
 tests/golden/; tests/test_oracle.py checks this port against those vectors bit for
 bit (features, masks, argmax actions) and within fp32 tolerance (Q values, update).
 tests/test_oracle_vs_reference.py additionally compares against the live reference
-when /root/reference exists.
+wherever it was staged into oracle/_ref (oracle/ref_stage.py; the build container and,
+because the snapshot carries it, the GPU box).
 
 Third-party arithmetic: like the reference, the MLP / Huber / autograd / Adam are
 torch CPU fp32 (reference pins torch 2.6.0, poetry.lock:3316; this image has 2.11).

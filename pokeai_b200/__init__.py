@@ -12,6 +12,7 @@ _LAZY = {
     "AgentTrain": ".agent", "ReplayBuffer": ".replay_buffer", "ReplayBufferItem": ".replay_buffer",
     "Trainer": ".trainer", "DQN_DEFAULT_PARAMS": ".trainer", "DecisionSession": ".session", "DecisionPipeline": ".session", "pinned_records": ".session",
     "PartyEvaluator": ".party_evaluator", "PartyEvaluatorQuick": ".party_evaluator",
+    "LockStepDriver": ".lockstep", "SyntheticBattle": ".lockstep",
     "PackedRLPolicy": ".protocol", "pack_request": ".protocol", "get_possible_actions": ".protocol", "pack_requests": ".protocol",
 }
 

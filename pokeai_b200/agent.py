@@ -38,21 +38,22 @@ class Agent:
     def _session(self, n: int):
         s = self._feature_extractor.session(n)
         m = self._model
-        # cheap change detector (the full key lives in MLPModel.prepared): parameter versions and storage pointers
+        # cheap change detector (the full key lives in MLPModel.prepared): generation, parameter versions, storage
+        # pointers -- and which agent pointed the (shared) session last: two agents whose models have no `.prepared`
+        # (a reference nn.Module) would otherwise both see "nothing changed" while the session holds the other's weights
         plist = self.__dict__.get("_plist")
         if plist is None:
             plist = self._plist = list(m.parameters()) + list(m.buffers())
-        fast = (id(s),) + tuple(p._version for p in plist) + tuple(p.data_ptr() for p in plist)
-        if self.__dict__.get("_fast_key") == fast and getattr(s, "_prepared_ref", None) is self.__dict__.get("_last_prep"):
-            return s  # same parameters, and no other agent has re-pointed the shared session since
+        fast = (id(s), getattr(m, "_generation", 0)) + tuple(p._version for p in plist) + tuple(p.data_ptr() for p in plist)
+        if self.__dict__.get("_fast_key") == fast and getattr(s, "_weights_owner", None) is m:
+            return s  # same parameters, and no other model has been loaded into the shared session since
         if hasattr(m, "prepared"):
             prep = m.prepared(s.device)  # rebuilt (a NEW tensor) only when a parameter changed
             if getattr(s, "_prepared_ref", None) is not prep:  # (re)pointing synchronises: do it only on a change
                 s.use_prepared(prep, m.n_layers, m.n_channels)
-            self._last_prep = prep
         else:
             s.load_model(m)
-            self._last_prep = None
+        s._weights_owner = m
         self._fast_key = fast
         return s
 
@@ -149,15 +150,18 @@ class AgentTrain(Agent):
         self._last_state = None
         self._last_action_mask = None
         self._last_action = 0
+        self.pending_record = None
 
-    def act(self, obs, reward: float) -> int:
-        """agent_train.py:24-37.  The two numpy global-RNG draws happen on the host in the reference's
-        order (np.random.random(), then np.random.choice over the legal slots when exploring), so a
-        seeded run makes the same explore/exploit choices as the reference."""
-        n = 1
-        s = self._session(n)
-        self._feature_extractor.pack(obs if isinstance(obs, np.ndarray) else [obs], out=s.packed)
-        packed = s.packed[0].copy()
+    def begin_act(self, obs, reward: float) -> Optional[int]:
+        """First half of `act` (agent_train.py:24-31): pack the observation, append the transition that ended with it
+        to the replay buffer, and make the exploration draw.  Returns the random action when exploring, else None:
+        the caller obtains the greedy action for `self.pending_record` from the model (alone, or batched with other
+        battles by `LockStepDriver`) and passes it to `finish_act`.
+        The two numpy global-RNG draws happen on the host in the reference's order (np.random.random(), then
+        np.random.choice over the legal slots when exploring), so a seeded run makes the same explore/exploit choices
+        as the reference."""
+        rec = self._feature_extractor.pack(obs if isinstance(obs, np.ndarray) else [obs])
+        packed = rec[0].copy()
         n_act = int(packed["n_act"])
         action_mask = np.zeros((self._feature_extractor.output_dim,), dtype=np.int32)
         action_mask[:n_act] = 1
@@ -165,16 +169,30 @@ class AgentTrain(Agent):
             self._replay_buffer.append(
                 ReplayBufferItem(self._last_state, self._last_action_mask, self._last_action, packed, action_mask,
                                  reward))
-        if np.random.random() < self._epsilon:
-            action = self._act_random(None, action_mask)
-        else:
-            q, a = s.decide(n)
-            action = int(a[0])
-            self._log_q(q[0], n_act, action)
         self._last_state = packed
         self._last_action_mask = action_mask
-        self._last_action = action
-        return action
+        self.pending_record = packed
+        if np.random.random() < self._epsilon:
+            return self._act_random(None, action_mask)
+        return None
+
+    def finish_act(self, action: int) -> int:
+        """Second half of `act` (agent_train.py:32-36): remember the action taken in the pending state."""
+        self._last_action = int(action)
+        self.pending_record = None
+        return self._last_action
+
+    def act(self, obs, reward: float) -> int:
+        """agent_train.py:24-37.  The greedy branch goes through `q_and_action_batch`, i.e. the fused small-net kernel
+        or, for a wide model, the tensor-core path."""
+        action = self.begin_act(obs, reward)
+        if action is None:
+            rec = np.zeros(1, dtype=self.pending_record.dtype)
+            rec[0] = self.pending_record
+            q, a = self.q_and_action_batch(rec)
+            action = int(a[0])
+            self._log_q(q[0], int(rec["n_act"][0]), action)
+        return self.finish_act(action)
 
     def stop_episode(self, reward: float) -> None:
         self._replay_buffer.append(

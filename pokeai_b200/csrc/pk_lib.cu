@@ -48,9 +48,15 @@ struct PkGlobal {
   int decide_pair = 1;
   int decide_tc = 0;  // 64-channel nets: hidden layers on tcgen05 (PK_DECIDE_TC: 0 never (measured best), 1 when features are written, 2 always)
   int hidden_tc = 0;
-  int pdl = 1;        // pk_decide launches carry the programmatic-stream-serialization attribute (PK_PDL)
+  // programmatic dependent launch (the record-only prologue of a pk_decide / pk_encode launch overlaps the tail of the
+  // previous kernel of the stream): OFF for the public device-pointer entry points unless the caller opts in
+  // (pk_set_overlap_launches / PK_PDL=1: the records must not be produced by the preceding kernel), ON for the host-buffer
+  // sessions, whose records always arrive from host memory (PK_PDL_SESSION=0 turns that off)
+  int pdl = 0;
+  int pdl_session = 1;
   int dense_warps = 16;  // warps per CTA of the dense-input forward (PK_DENSE_WARPS; kernel iteration only)
   int zero_copy = 1;  // host-buffer calls: kernels read / write pinned host buffers directly (PK_ZERO_COPY)
+  int peer_timeout_ms = 30000;  // pk_peer_clamp_adam: how long a rank waits for its peers' gradients (PK_PEER_TIMEOUT_MS)
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
@@ -101,7 +107,9 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.ctas_per_sm = env_int("PK_CTAS_PER_SM", 1, 1, 4);
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
   g.hidden_tc = env_int("PK_HIDDEN_TC", 0, 0, 1);  // 64-channel hidden layers on the 3xTF32 mma.sync path (measured: no gain)
-  g.pdl = env_int("PK_PDL", 1, 0, 1);
+  g.pdl = env_int("PK_PDL", 0, 0, 1);
+  g.pdl_session = env_int("PK_PDL_SESSION", 1, 0, 1);
+  g.peer_timeout_ms = env_int("PK_PEER_TIMEOUT_MS", 30000, 1, 3600000);
   g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 2);
   g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
   g.wide_side = env_int("PK_WIDE_SIDE", 1, 0, 1);
@@ -227,7 +235,7 @@ static inline int pk_at_for(int A) { return A <= 4 ? 4 : (A <= 6 ? 6 : 9); }
 
 static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepared, int n_layers, int n_channels,
                           float* feat, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
-                          cudaStream_t st) {
+                          cudaStream_t st, bool pdl) {
   PK_CHECK_INIT();
   PK_REQUIRE(B >= 0, "negative batch");
   PK_REQUIRE(A >= 1 && A <= PK_MAX_ACTIONS, "A=%d not in 1..%d", A, PK_MAX_ACTIONS);
@@ -277,7 +285,7 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
   {                                                                                                               \
     int rc_ = pk_set_smem(pk_decide_tc_kernel<A_>, tplan.total);                                                  \
     if (rc_) return rc_;                                                                                          \
-    PK_CUDA(pk_launch_pdl(pk_decide_tc_kernel<A_>, tgrid, PKT_WARPS * 32, tplan.total, st, g.pdl != 0, pk, B,     \
+    PK_CUDA(pk_launch_pdl(pk_decide_tc_kernel<A_>, tgrid, PKT_WARPS * 32, tplan.total, st, pdl, pk, B,            \
                           prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0, (unsigned)g.max_smem));      \
   }
       switch (A) {
@@ -356,13 +364,13 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
         int rc_ = pk_set_smem(pk_decide_kernel<2, A_, 512, true>, plan.total);                                \
         if (rc_) return rc_;                                                                                  \
         PK_CUDA(pk_launch_pdl(pk_decide_kernel<2, A_, 512, true>, grid, nwarps * 32, plan.total, st,          \
-                              g.pdl != 0, pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0)); \
+                              pdl, pk, B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0));        \
         break;                                                                                                \
       }                                                                                                       \
     }                                                                                                         \
     int rc_ = pk_set_smem(pk_decide_kernel<C_, A_, 512>, plan.total);                                         \
     if (rc_) return rc_;                                                                                      \
-    PK_CUDA(pk_launch_pdl(pk_decide_kernel<C_, A_, 512>, grid, nwarps * 32, plan.total, st, g.pdl != 0, pk,   \
+    PK_CUDA(pk_launch_pdl(pk_decide_kernel<C_, A_, 512>, grid, nwarps * 32, plan.total, st, pdl, pk,          \
                           B, prepared, lay, feat, mask, q, action, ps, use_tma ? 1 : 0));                     \
   }
 #define PK_LAUNCH_DECIDE_A(C_)                                        \
@@ -388,14 +396,16 @@ static int pk_decide_impl(const pk_obs* packed, int B, int A, const float* prepa
 }
 
 extern "C" int pk_encode(const pk_obs* packed, int B, int A, float* feat, int32_t* mask, void* stream) {
-  return pk_decide_impl(packed, B, A, nullptr, 0, 0, feat, mask, nullptr, nullptr, nullptr, (cudaStream_t)stream);
+  return pk_decide_impl(packed, B, A, nullptr, 0, 0, feat, mask, nullptr, nullptr, nullptr, (cudaStream_t)stream,
+                        g.pdl != 0);
 }
 
 extern "C" int pk_decide(const pk_obs* packed, int B, int A, const float* prepared, int n_layers, int n_channels,
                          float* feat, int32_t* mask, float* q, int32_t* action, const pk_select_params* sel,
                          void* stream) {
   PK_REQUIRE(prepared != nullptr, "pk_decide: null prepared weights");
-  return pk_decide_impl(packed, B, A, prepared, n_layers, n_channels, feat, mask, q, action, sel, (cudaStream_t)stream);
+  return pk_decide_impl(packed, B, A, prepared, n_layers, n_channels, feat, mask, q, action, sel, (cudaStream_t)stream,
+                        g.pdl != 0);
 }
 
 extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channels, int in_channels, const float* feat,
@@ -648,7 +658,7 @@ extern "C" int pk_session_submit_host(pk_session* s, const pk_obs* packed_host, 
     sp.u_pick = s->d_u_pick;
   }
   int rc = pk_decide_impl(in_dev, B, s->A, s->prepared, s->n_layers, s->n_channels, s->d_feat, s->d_mask, q_dev, act_dev,
-                          &sp, s->stream);
+                          &sp, s->stream, g.pdl_session != 0);
   if (rc) return rc;
   if (q_host && !q_direct)
     PK_CUDA(cudaMemcpyAsync(q_host, s->d_q, (size_t)B * s->A * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
@@ -681,7 +691,8 @@ extern "C" int pk_session_encode_host(pk_session* s, const pk_obs* packed_host, 
   PK_REQUIRE(B >= 0 && B <= s->max_batch, "batch %d exceeds the session capacity %d", B, s->max_batch);
   if (B == 0) return PK_OK;
   PK_CUDA(cudaMemcpyAsync(s->d_packed, packed_host, (size_t)B * sizeof(pk_obs), cudaMemcpyHostToDevice, s->stream));
-  int rc = pk_decide_impl(s->d_packed, B, s->A, nullptr, 0, 0, s->d_feat, s->d_mask, nullptr, nullptr, nullptr, s->stream);
+  int rc = pk_decide_impl(s->d_packed, B, s->A, nullptr, 0, 0, s->d_feat, s->d_mask, nullptr, nullptr, nullptr, s->stream,
+                          g.pdl_session != 0);
   if (rc) return rc;
   return pk_session_fetch(s, B, feat_host, mask_host);
 }

@@ -387,6 +387,7 @@ struct PkPeers {
   unsigned* flags[PK_MAX_PEERS];    // every rank's flag words; flags[d][r] = last epoch rank r published to rank d
   int rank, world;
   unsigned epoch;
+  unsigned long long timeout_ns;    // how long a CTA waits for the peers' flags before it gives up (PK_PEER_TIMEOUT_MS)
 };
 __device__ __forceinline__ unsigned pk_ld_acquire_sys(const unsigned* p) {
   unsigned v;
@@ -406,17 +407,28 @@ __global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe
     __threadfence_system();
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pe.flags[threadIdx.x] + pe.rank), "r"(pe.epoch) : "memory");
   }
-  if (threadIdx.x < pe.world) {  // every CTA waits on this rank's own flag words (local memory)
+  // Every CTA waits on this rank's own flag words (local memory).  A rank that never arrives must not hang the GPU
+  // for ever: after `timeout_ns` the CTA gives up -- it raises loss_status[1] and returns WITHOUT touching params, m,
+  // v or prepared (the decision is shared through shared memory, so a CTA is all-or-nothing).  The host checks the
+  // flag after every step (Trainer raises); a step with loss_status[1] != 0 must be treated as not taken.
+  __shared__ int s_timed_out;
+  if (threadIdx.x == 0) s_timed_out = 0;
+  __syncthreads();
+  if (threadIdx.x < pe.world) {
     const unsigned* f = pe.flags[pe.rank] + threadIdx.x;
     const unsigned long long t0 = pk_globaltimer();
     while ((int)(pk_ld_acquire_sys(f) - pe.epoch) < 0) {
-      if (pk_globaltimer() - t0 > 2000000000ull) {
-        if (loss_status != nullptr) loss_status[1] = 1.0f;
+      if (pk_globaltimer() - t0 > pe.timeout_ns) {
+        s_timed_out = 1;
         break;
       }
     }
   }
   __syncthreads();
+  if (s_timed_out) {
+    if (threadIdx.x == 0 && loss_status != nullptr) loss_status[1] = 1.0f;
+    return;
+  }
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i > P.total) return;
   float gs = 0.0f;

@@ -36,6 +36,9 @@ class MLPModel(nn.Module):
         self.n_channels = int(n_channels)
         self._prepared: Optional[torch.Tensor] = None
         self._prepared_key: Optional[Tuple] = None
+        # bumped by whoever rewrites the parameters through raw pointers (Trainer's update kernels): torch's version
+        # counters do not see such writes, and every cache of derived weights keys on `weights_key()`
+        self._generation = 0
 
     # -- folded parameters --------------------------------------------------------------------
     def folded_state_dict(self) -> dict:
@@ -56,13 +59,29 @@ class MLPModel(nn.Module):
         sd["output.bias"] = self.output.bias.detach()
         return sd
 
+    def weights_key(self) -> Tuple:
+        """Changes whenever the parameters may have: storage pointers, torch version counters, and the generation
+        counter that in-place kernel updates bump (`mark_updated`)."""
+        return (self._generation,) + tuple((p.data_ptr(), p._version) for p in self.parameters()) + \
+            tuple((b.data_ptr(), b._version) for b in self.buffers())
+
+    def mark_updated(self, prepared: Optional[torch.Tensor] = None) -> None:
+        """The parameters were rewritten behind torch's back (pk_clamp_adam / pk_peer_clamp_adam through raw
+        pointers).  `prepared`: the up-to-date prepared copy the same kernel refreshed, adopted as this model's."""
+        self._generation += 1
+        if prepared is not None:
+            self._prepared = prepared
+            self._prepared_key = (str(prepared.device),) + self.weights_key()
+        else:
+            self._prepared = None
+            self._prepared_key = None
+
     def prepared(self, device) -> torch.Tensor:
         """The kernels' transposed / padded copy of the weights on `device`, rebuilt when any
-        parameter changes (tracked through the tensors' version counters)."""
+        parameter changes (`weights_key`)."""
         from . import ops
         device = torch.device(device)
-        key = (str(device),) + tuple((p.data_ptr(), p._version) for p in self.parameters()) + \
-              tuple((b.data_ptr(), b._version) for b in self.buffers())
+        key = (str(device),) + self.weights_key()
         if self._prepared is None or self._prepared_key != key:
             if self.bn and self.training:
                 raise NotImplementedError("train-mode BatchNorm has no kernel; call .eval() (bn is folded)")

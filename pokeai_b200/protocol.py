@@ -15,12 +15,14 @@ exceptions: KeyError on unknown names or a request without 'active', ValueError 
 """
 from __future__ import annotations
 
+import struct
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from .packed import FLAG_FORCE, FLAG_SWITCH, PK_OBS_DTYPE, pack_state_into
-from .tables import MAX_ACTIONS, MAX_MOVES, Tables, load_tables
+from .observation import RANK_KEYS
+from .packed import FLAG_FORCE, FLAG_SWITCH, PK_OBS_BYTES, PK_OBS_DTYPE, _status_code, pack_state_into
+from .tables import MAX_ACTIONS, MAX_MOVES, WEATHER_CODE, Tables, load_tables
 
 
 def _active_move_id(move_id: str, name: str) -> str:
@@ -142,6 +144,71 @@ def pack_requests(pairs: Sequence[Tuple[object, dict]], tables: Optional[Tables]
         pack_state_into(out[i], bs, tables)
         keys.append(pack_actions_into(out[i], request, tables, max_actions))
     return out, keys
+
+
+_HEADER = struct.Struct("<2B2B2H2H2B14b4B")   # offsets 0..31 of pk_obs (include/pokeai_b200.h)
+_ACTION = struct.Struct("<4B4H")               # one pk_action
+assert _HEADER.size == 32 and _ACTION.size == 12
+_ZERO_RECORD = bytes(PK_OBS_BYTES)
+
+
+def pack_request_into(buf, offset: int, battle_status, request: dict, tables: Tables,
+                      max_actions: int = MAX_ACTIONS) -> List[str]:
+    """`pack_request` for a driver's inner loop: writes the 144-byte record at `buf[offset:]` (any writable buffer,
+    e.g. the bytes of a `pinned_records` array) with a dozen `struct.pack_into` calls instead of ~100 numpy field
+    assignments (5 us instead of 34 us per request), and returns the simulator keys.  Same bytes, same order, same
+    exceptions as `pack_state_into` + `pack_actions_into` (tests/test_protocol.py)."""
+    bs = battle_status
+    sf, so = bs.side_statuses[bs.side_friend], bs.side_statuses[bs.side_opponent]
+    af, ao = sf.active, so.active
+    assert af is not None and ao is not None  # state_feature_extractor.py:133,148,161,177
+    if sf.total_pokes == 0 or so.total_pokes == 0 or af.hp_max == 0 or ao.hp_max == 0:
+        raise ZeroDivisionError("division by zero")  # the reference divides in Python (:122,:150)
+    rf, ro = af.ranks, ao.ranks
+    force_switch = bool(request.get("forceSwitch"))
+    if not force_switch:
+        active = request["active"]
+        trapped = active[0].get("trapped")
+    else:
+        active, trapped = None, False
+    sp_idx, mv_idx, it_idx = tables.species_name_to_idx, tables.move_to_idx, tables.item_to_idx
+    opp = sp_idx[ao.species]  # KeyError like dex.get_pokedex_by_name
+    buf[offset:offset + PK_OBS_BYTES] = _ZERO_RECORD
+    keys: List[str] = []
+    pos = offset + 32
+    for poke_idx, member in enumerate(request["side"]["pokemon"]):
+        species = sp_idx[member["details"].split(",")[0]]
+        if member["active"]:
+            if force_switch:
+                continue
+            item = it_idx[member["item"]]
+            for move_idx, move in enumerate(active[0]["moves"]):
+                if move.get("disabled"):
+                    continue
+                if len(keys) >= max_actions:
+                    raise ValueError(f"more than {max_actions} possible actions")
+                _ACTION.pack_into(buf, pos, 0, species, item, 1, mv_idx[_active_move_id(move["id"], move["move"])], 0, 0, 0)
+                pos += 12
+                keys.append(f"move {move_idx + 1}")
+        else:
+            if member["condition"].endswith(" fnt") or trapped:
+                continue
+            moves = member["moves"]
+            if len(moves) > MAX_MOVES:
+                raise ValueError("more than 4 moves on one action")
+            if len(keys) >= max_actions:
+                raise ValueError(f"more than {max_actions} possible actions")
+            m = [mv_idx[_side_move_id(x)] for x in moves]
+            m += [0] * (MAX_MOVES - len(m))
+            _ACTION.pack_into(buf, pos, FLAG_SWITCH | (FLAG_FORCE if force_switch else 0), species, it_idx[member["item"]],
+                              len(moves), *m)
+            pos += 12
+            keys.append(f"switch {poke_idx + 1}")
+    _HEADER.pack_into(buf, offset, sf.remaining_pokes, so.remaining_pokes, sf.total_pokes, so.total_pokes,
+                      af.hp_current, ao.hp_current, af.hp_max, ao.hp_max, _status_code(af.status), _status_code(ao.status),
+                      *[rf[k] for k in RANK_KEYS], *[ro[k] for k in RANK_KEYS], opp, WEATHER_CODE.get(bs.weather, 0),
+                      len(keys), 0)
+    return keys
 
 
 class PackedRLPolicy:

@@ -196,7 +196,7 @@ class DecisionPipeline:
         if ps is None or self._plist_model is not m:
             ps = self._plist = list(m.parameters()) + list(m.buffers())
             self._plist_model = m
-        version = [p._version for p in ps] + [p.data_ptr() for p in ps]
+        version = [getattr(m, "_generation", 0)] + [p._version for p in ps] + [p.data_ptr() for p in ps]
         if version == self._version:
             return
         for s in self._sessions:  # batches in flight still read the old weights: let them finish first

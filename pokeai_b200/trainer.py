@@ -193,7 +193,7 @@ class Trainer:
         model.eval()
         if not self._wide:  # wide models are prepared by the agent's WideRunner
             model._prepared = self._prepared.clone()
-            model._prepared_key = (str(self.device),) + tuple((p.data_ptr(), p._version) for p in model.parameters())
+            model._prepared_key = (str(self.device),) + model.weights_key()
         return model
 
     # -- checkpoints (trainer.py:73-121) ---------------------------------------------------------------
@@ -256,6 +256,14 @@ class Trainer:
 
     def get_val_agent(self):
         return AgentVal(self._snapshot_model(), self.feature_extractor)
+
+    def get_train_agents(self, n: int):
+        """`n` training agents for `n` concurrent battles that share ONE snapshot of the online network (each keeps its
+        own replay buffer and episode state), so that `LockStepDriver` can decide for all of them in one launch.
+        Equivalent to `n` calls of `get_train_agent()` made at the same `total_steps` (trainer.py:123-128)."""
+        epsilon = max(math.pow(1.0 - self.epsilon_decay, self.total_steps) * self.epsilon, self.epsilon_min)
+        model = self._snapshot_model()
+        return [AgentTrain(model, self.feature_extractor, epsilon) for _ in range(n)]
 
     def extend_replay_buffer(self, buffer: ReplayBuffer):
         steps = len(buffer)
@@ -339,7 +347,11 @@ class Trainer:
                                  opt.lr, opt.betas, opt.eps, prepared=self._prepared, grad_sum=self._grad)
             ls = px.loss_status.tolist()
             if ls[1] != 0.0:
-                raise RuntimeError("peer gradient exchange: a rank did not arrive within the time limit")
+                # the kernel gave up without writing parameters or Adam moments: undo the step count and say so
+                opt.step_count -= 1
+                raise RuntimeError("peer gradient exchange: a rank did not arrive within the time limit "
+                                   "(PK_PEER_TIMEOUT_MS); this update was NOT applied")
+            self.model.mark_updated(self._prepared)
             return float(ls[0])
         if dist is not None:  # sum of shard gradients == gradient of the global mean loss; clamp comes after
             from .dist import allreduce_sum_
@@ -347,6 +359,7 @@ class Trainer:
         N.check(lib.pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
                                   opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
                                   opt.betas[1], opt.eps, opt.step_count, self._prepared.data_ptr(), stream))
+        self.model.mark_updated(self._prepared)  # trainer.model(x) / Agent(trainer.model, fe) see the new weights
         return float(self._loss.item())
 
     def _peer_exchange(self, dist):
@@ -406,6 +419,7 @@ class Trainer:
                                       opt.betas[1], opt.eps, opt.step_count, None,
                                       torch.cuda.current_stream(self.device).cuda_stream))
         self._refresh_prepared()
+        self.model.mark_updated()  # wide: agents re-derive their bf16 copies from the new parameters
 
     def _update_wide(self, state, next_state, action, reward, terminal, n_global: int) -> float:
         """The same Double-DQN step for a wide network (tensor-core path): Q(s, a) of the CHOSEN column with the
@@ -461,3 +475,4 @@ class Trainer:
     def _target_update(self):  # trainer.py:197-198
         self._flat_target.copy_(self._flat)
         self._prepared_target.copy_(self._prepared)
+        self.target_model.mark_updated(None if self._wide else self._prepared_target)

@@ -114,7 +114,7 @@ class WideRunner:
 
     def _ensure(self, n: int) -> None:
         m = self.model
-        key = tuple((p.data_ptr(), p._version) for p in m.parameters())
+        key = (getattr(m, "_generation", 0),) + tuple((p.data_ptr(), p._version) for p in m.parameters())
         if self._prepared is None or key != self._key:
             self._prepared = prepare_wide(m.folded_state_dict(), self.device)[0]
             self._key = key

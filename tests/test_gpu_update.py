@@ -248,6 +248,46 @@ def test_trainer_update_equals_oracle_on_the_same_minibatch(tables):
     assert torch.equal(ops.prepare_from_flat(tr._flat, 2, 64, 617), tr._prepared)
 
 
+@pytest.mark.parametrize("nl,H", [(2, 64), (2, 256)])
+def test_trainer_model_follows_in_place_updates(tables, nl, H):
+    """the update kernels rewrite the parameters through raw pointers (torch's version counters do not move):
+    trainer.model(x), an agent built on trainer.model and a DecisionPipeline on it must still see every step"""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200.agent import AgentVal
+    from pokeai_b200.packed import synth_packed
+    from pokeai_b200.trainer import Trainer
+    torch.manual_seed(2)
+    np.random.seed(2)
+    random.seed(2)
+    tr = Trainer({"n_layers": nl, "n_channels": H}, {"batch_size": 16, "first_update_steps": 20, "lr": 1e-2},
+                 {"party_size": 3})
+    _fill_by_self_play(tr, tables, n_episodes=3, steps_per_episode=8, seed=3)
+    rec = synth_packed(40, seed=77, party_size=3, kind="ragged", tables=tables)
+    fo, mo = packed_oracle.encode(rec, 3, tables)
+    x = torch.from_numpy(fo).to(tr.device)
+    agent = AgentVal(tr.model, tr.feature_extractor)
+    tol = dict(rtol=1e-5, atol=1e-5) if H == 64 else dict(rtol=0, atol=3e-2)  # wide nets decide in bf16
+
+    def check():
+        sd = {k: v.detach().cpu().clone() for k, v in tr.model.state_dict().items()}
+        with torch.no_grad():
+            qo = ref_port.mlp_forward(sd, torch.from_numpy(fo)).numpy()
+        if H == 64:
+            np.testing.assert_allclose(tr.model(x).cpu().numpy(), qo, **tol)
+        q, _ = agent.q_and_action_batch(rec)
+        np.testing.assert_allclose(np.array(q), qo, **tol)
+        return qo
+
+    q0 = check()
+    for _ in range(3):
+        tr._update()
+    q1 = check()
+    assert np.abs(q1 - q0).max() > 1e-3  # the weights really moved
+    tr._target_update()
+    tr._update()
+    check()
+
+
 def test_trainer_schedule_checkpoint_and_agents(tables):
     from pokeai_b200.trainer import Trainer, DQN_DEFAULT_PARAMS
     assert DQN_DEFAULT_PARAMS["batch_size"] == 32 and DQN_DEFAULT_PARAMS["target_update"] == 100

@@ -49,6 +49,26 @@ def test_pack_request_equals_possible_actions_route(cases, statuses, tables):
     assert recs[7].tobytes() == pack_request(*pairs[7], tables)[0].tobytes()
 
 
+def test_struct_packer_writes_the_same_bytes(cases, statuses, tables):
+    """pack_request_into (struct.pack_into, the lock-step driver's packer) == pack_request, byte for byte"""
+    from pokeai_b200.packed import PK_OBS_BYTES
+    from pokeai_b200.protocol import pack_request, pack_request_into
+    buf = bytearray(b"\xff" * (3 * PK_OBS_BYTES))
+    for i, c in enumerate(cases):
+        bs = statuses[i % len(statuses)]
+        rec, keys = pack_request(bs, c["request"], tables)
+        got = pack_request_into(buf, PK_OBS_BYTES, bs, c["request"], tables)
+        assert got == keys, i
+        assert bytes(buf[PK_OBS_BYTES:2 * PK_OBS_BYTES]) == rec.tobytes(), i
+        assert buf[:PK_OBS_BYTES] == b"\xff" * PK_OBS_BYTES and buf[2 * PK_OBS_BYTES:] == b"\xff" * PK_OBS_BYTES
+    with pytest.raises(ValueError):
+        pack_request_into(buf, 0, statuses[0], [c for c in cases if len(c["possible_actions"]) > 3][0]["request"], tables, 3)
+    with pytest.raises(KeyError):
+        bad = copy.deepcopy(cases[0]["request"])
+        bad["side"]["pokemon"][0]["details"] = "Missingno, L50"
+        pack_request_into(buf, 0, statuses[0], bad, tables)
+
+
 def test_get_possible_actions_equals_reference(cases, tables):
     """the restated get_possible_actions against the reference's outputs, field by field"""
     from pokeai_b200.protocol import get_possible_actions

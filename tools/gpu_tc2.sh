@@ -15,4 +15,4 @@ for r in d['roofline']['secondary'] or []:
     print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k not in ('config',)}, '|', r.get('config','')[:70])
 PY
 tail -5 $OUT/bench_r02.err
-echo "== bench reference"; timeout 600 python bench.py --impl reference --steps 5 --warmup 1 | cut -c1-400
+echo "== bench reference"; timeout 600 python bench.py --impl reference --steps 5 --warmup 1 | cut -c1-400; cp gpurun_out/bench_r02.json gpurun_out/bench_n1_r02.json
