@@ -246,3 +246,23 @@ __device__ __forceinline__ float pk_ldg_f(const float* p) { return __ldg(p); }
 // programmatic dependent launch (cudaLaunchAttributeProgrammaticStreamSerialization)
 __device__ __forceinline__ void pk_grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pk_grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// inverse of pk_flat_to_prepared for the inference part of the prepared layout: position p in [0, L.total) -> flat
+// parameter index, or -1 for padding / the zero row
+__host__ __device__ inline int pk_prepared_to_flat(const PkParamLayout& P, const PkLayout& L, unsigned p) {
+  const unsigned HP = (unsigned)L.HP, H = (unsigned)P.H;
+  if (p < L.b[0]) {  // W0^T [C + 1][HP]
+    const unsigned k = p / HP, j = p - k * HP;
+    return (k < (unsigned)P.C && j < H) ? (int)(P.w[0] + j * (unsigned)P.C + k) : -1;
+  }
+  for (int l = 0; l < P.n_layers; ++l) {
+    if (p >= L.b[l] && p < L.b[l] + HP) return (p - L.b[l] < H) ? (int)(P.b[l] + (p - L.b[l])) : -1;
+    if (l > 0 && p >= L.wl[l] && p < L.wl[l] + HP * HP) {
+      const unsigned e = p - L.wl[l], k = e / HP, j = e - k * HP;
+      return (k < H && j < H) ? (int)(P.w[l] + j * H + k) : -1;
+    }
+  }
+  if (p >= L.wout && p < L.wout + HP) return (p - L.wout < H) ? (int)(P.wout + (p - L.wout)) : -1;
+  if (p == L.bout) return (int)P.bout;
+  return -1;
+}

@@ -18,13 +18,18 @@
 #define PK2_IDX_BYTES (2 * PK_WARP_IDX_BYTES)
 #define PK2_FIXED_BYTES (PK2_REC_BYTES + PK2_SV_BYTES + PK2_IDX_BYTES)
 
-__host__ __device__ inline PkSmemPlan pk2_smem_plan(const PkLayout& lay, int A, int nwarps, bool zero_tile) {
+// `dual`: a second network (the target network of Double DQN) is staged behind the first; its tail / state rows
+// start PK2_NET_BYTES(lay) after the first one's
+#define PK2_NET_BYTES(lay) (((lay).total - (lay).b[0]) * 4u + (unsigned)PK_N_STATE * (lay).HP * 4u)
+__host__ __device__ inline PkSmemPlan pk2_smem_plan(const PkLayout& lay, int A, int nwarps, bool zero_tile,
+                                                    bool dual = false) {
   PkSmemPlan p;
   unsigned o = 0;
   p.tail = o;
   o += (lay.total - lay.b[0]) * 4u;
   p.w1s = o;
   o += (unsigned)PK_N_STATE * lay.HP * 4u;
+  if (dual) o += PK2_NET_BYTES(lay);
   p.warp_area = o;
   p.warp_stride = PK2_FIXED_BYTES + 2u * (unsigned)A * lay.HP * 4u;
   o += p.warp_stride * nwarps;
@@ -124,18 +129,23 @@ __device__ __forceinline__ void pk2_hidden(const float* __restrict__ WT, const f
   }
 }
 
-template <int CH, int A>
+// DUAL (the next-state pass of the Double-DQN update, trainer.py:169-177): a second network `prep2` (the target) is
+// staged too, and after the masked argmax a* of the first (online) network's Q the kernel evaluates the target network
+// for column a* ONLY and stores v_out[b] = Q_target(s', a*) -- the records are parsed once, and the target pass costs
+// one column instead of nine.
+template <int CH, int A, bool DUAL = false>
 __global__ void __launch_bounds__(512, 1)
 pk_decide2_kernel(const uint4* __restrict__ packed, int B, const float* __restrict__ prep, PkLayout lay,
                   float* __restrict__ feat, int* __restrict__ mask, float* __restrict__ q,
-                  int* __restrict__ action, PkSelect sel, int zero_by_tma) {
+                  int* __restrict__ action, PkSelect sel, int zero_by_tma, const float* __restrict__ prep2 = nullptr,
+                  float* __restrict__ v_out = nullptr) {
   constexpr int HP = 16 * CH;
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int half = lane >> 4, hl = lane & 15;
   const int L = lay.C * A;
   const bool use_tma = feat != nullptr && (zero_by_tma & 1) != 0;
-  const PkSmemPlan plan = pk2_smem_plan(lay, A, nwarps, use_tma);
+  const PkSmemPlan plan = pk2_smem_plan(lay, A, nwarps, use_tma, DUAL);
 
   unsigned long long* tr = sel.trace;
   const int tslot = blockIdx.x * nwarps + warp;
@@ -145,9 +155,13 @@ pk_decide2_kernel(const uint4* __restrict__ packed, int B, const float* __restri
     const uint32_t tail_bytes = (lay.total - lay.b[0]) * 4u, w1s_bytes = (uint32_t)PK_N_STATE * lay.HP * 4u;
     pk_mbar_init(wbar, 1);
     pk_fence_mbar_init();
-    pk_mbar_expect_tx(wbar, tail_bytes + w1s_bytes);
+    pk_mbar_expect_tx(wbar, (tail_bytes + w1s_bytes) * (DUAL ? 2u : 1u));
     pk_bulk_load(smem + plan.tail, prep + lay.b[0], tail_bytes, wbar);
     pk_bulk_load(smem + plan.w1s, prep + lay.w1t, w1s_bytes, wbar);
+    if (DUAL) {
+      pk_bulk_load(smem + plan.tail + PK2_NET_BYTES(lay), prep2 + lay.b[0], tail_bytes, wbar);
+      pk_bulk_load(smem + plan.w1s + PK2_NET_BYTES(lay), prep2 + lay.w1t, w1s_bytes, wbar);
+    }
   }
   const float* zero_tile = nullptr;
   if (use_tma) {
@@ -350,10 +364,89 @@ pk_decide2_kernel(const uint4* __restrict__ packed, int B, const float* __restri
     for (int c = 0; c < A; ++c)
       if (hl == c) myq = qv[c];
     if (q != nullptr && valid_own && hl < A) q[b_own * A + hl] = myq;
-    if (action != nullptr) {
+    if (action != nullptr || DUAL) {
       const bool writer = valid_own && hl == 0;
       const int act = pk_select_dev<A>(qv, (1u << n_act_own) - 1u, A, sel, valid_own ? b_own : 0, writer);
-      if (writer) action[b_own] = act;
+      if (writer && action != nullptr) action[b_own] = act;
+      if constexpr (DUAL) {
+        // ---- target network, column a* only: v = Q_target(s', a*) (trainer.py:175-177) ----
+        const float* t_tail = reinterpret_cast<const float*>(smem + plan.tail + PK2_NET_BYTES(lay));
+        const float* t_w1s = reinterpret_cast<const float*>(smem + plan.w1s + PK2_NET_BYTES(lay));
+        const float* w1t2 = prep2 + lay.w1t;
+        float gt[8][CH];
+        {
+          const int4 ia = *reinterpret_cast<const int4*>(idx_own + 8 * act);
+          const int4 ib = *reinterpret_cast<const int4*>(idx_own + 8 * act + 4);
+          pk2_gather<CH>(w1t2, ia.x, zero_row, CH * hl, HP, gt[0]);
+          pk2_gather<CH>(w1t2, ia.y, zero_row, CH * hl, HP, gt[1]);
+          pk2_gather<CH>(w1t2, ia.z, zero_row, CH * hl, HP, gt[2]);
+          pk2_gather<CH>(w1t2, ia.w, zero_row, CH * hl, HP, gt[3]);
+          pk2_gather<CH>(w1t2, ib.x, zero_row, CH * hl, HP, gt[4]);
+          pk2_gather<CH>(w1t2, ib.y, zero_row, CH * hl, HP, gt[5]);
+          pk2_gather<CH>(w1t2, ib.z, zero_row, CH * hl, HP, gt[6]);
+          pk2_gather<CH>(w1t2, ib.w, zero_row, CH * hl, HP, gt[7]);
+        }
+        float tb0[CH], tb1[CH];
+        pk2_lds<CH>(t_tail + CH * hl, tb0);
+#pragma unroll
+        for (int i = 0; i < CH; ++i) tb1[i] = 0.0f;
+        {
+          const float* wp = t_w1s + CH * hl;
+#pragma unroll 3
+          for (int k4 = 0; k4 < 48; k4 += 4) {
+            const float4 s4 = *reinterpret_cast<const float4*>(sv_own + k4);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const float x = kk == 0 ? s4.x : kk == 1 ? s4.y : kk == 2 ? s4.z : s4.w;
+              float w[CH];
+              pk2_lds<CH>(wp + (k4 + kk) * HP, w);
+              if (kk & 1) pk_fma_vec<CH>(tb1, w, x);
+              else pk_fma_vec<CH>(tb0, w, x);
+            }
+          }
+          const float2 s2 = *reinterpret_cast<const float2*>(sv_own + 48);
+          float w[CH];
+          pk2_lds<CH>(wp + 48 * HP, w);
+          pk_fma_vec<CH>(tb0, w, s2.x);
+          pk2_lds<CH>(wp + 49 * HP, w);
+          pk_fma_vec<CH>(tb1, w, s2.y);
+        }
+        float ht[CH];
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+          const float s01 = gt[0][i] + gt[1][i], s23 = gt[2][i] + gt[3][i];
+          const float s45 = gt[4][i] + gt[5][i], s67 = gt[6][i] + gt[7][i];
+          ht[i] = fmaxf((tb0[i] + tb1[i]) + ((s01 + s23) + (s45 + s67)), 0.0f);
+        }
+        for (int l = 1; l < lay.n_layers; ++l) {
+          __syncwarp();  // every lane is done with this half's hbuf (online pass / previous layer)
+          pk2_sts<CH>(hb_own + CH * hl, ht);
+          __syncwarp();
+          float at[CH];
+          pk2_lds<CH>(t_tail + (lay.b[l] - tb) + CH * hl, at);
+          const float* wp = t_tail + (lay.wl[l] - tb) + CH * hl;
+#pragma unroll 4
+          for (int k = 0; k < HP; k += 4) {
+            const float4 hv = *reinterpret_cast<const float4*>(hb_own + k);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              float w[CH];
+              pk2_lds<CH>(wp + (k + kk) * HP, w);
+              pk_fma_vec<CH>(at, w, kk == 0 ? hv.x : kk == 1 ? hv.y : kk == 2 ? hv.z : hv.w);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < CH; ++i) ht[i] = fmaxf(at[i], 0.0f);
+        }
+        float wo[CH];
+        pk2_lds<CH>(t_tail + (lay.wout - tb) + CH * hl, wo);
+        float sacc = 0.0f;
+#pragma unroll
+        for (int i = 0; i < CH; ++i) sacc = fmaf(wo[i], ht[i], sacc);
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) sacc += __shfl_xor_sync(0xffffffffu, sacc, o);
+        if (writer) v_out[b_own] = sacc + t_tail[lay.bout - tb];
+      }
     }
     pk_trace(tr, tslot, 8);
     if (gfeat0 != nullptr && use_tma) {

@@ -132,9 +132,10 @@ pk_decide_tc_kernel(const uint4* __restrict__ packed, int B, const float* __rest
                     float* __restrict__ feat, int* __restrict__ mask, float* __restrict__ q, int* __restrict__ action,
                     PkSelect sel, int zero_by_tma, unsigned max_smem) {
   constexpr int CPL = 2, HP = PKT_H, AT = A, NW = PKT_WARPS;
-  extern __shared__ unsigned char pkt_smem_raw[];
-  unsigned char* smem =
-      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(pkt_smem_raw) + 1023) & ~(uintptr_t)1023);
+  // SWIZZLE_128B operand tiles need 1024-byte alignment; asking for it in the declaration (instead of rounding a pointer
+  // up by hand) keeps the accesses in the shared address space (LDS / STS, not generic LD / ST)
+  extern __shared__ __align__(1024) unsigned char smem[];
+  if ((pk_smem_u32(smem) & 1023u) != 0u) __trap();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // group; TMEM lane quarter (warp % 4: the lanes this warp may read); the warp's 16-row half of that quarter
   const int grp = warp / PKT_GROUP, wq = warp & 3, wh = (warp / 4) & 1;

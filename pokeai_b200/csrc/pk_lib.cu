@@ -57,6 +57,7 @@ struct PkGlobal {
   int dense_warps = 16;  // warps per CTA of the dense-input forward (PK_DENSE_WARPS; kernel iteration only)
   int zero_copy = 1;  // host-buffer calls: kernels read / write pinned host buffers directly (PK_ZERO_COPY)
   int peer_timeout_ms = 30000;  // pk_peer_clamp_adam: how long a rank waits for its peers' gradients (PK_PEER_TIMEOUT_MS)
+  int upd_fused = 1;  // pk_dqn_grad: online + target next-state pass in one kernel (PK_UPDATE_FUSED)
   int ctas_per_sm = 1;
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
@@ -108,6 +109,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.zero_by_tma = env_int("PK_ZERO_TMA", 1, 0, 1);
   g.hidden_tc = env_int("PK_HIDDEN_TC", 0, 0, 1);  // 64-channel hidden layers on the 3xTF32 mma.sync path (measured: no gain)
   g.pdl = env_int("PK_PDL", 0, 0, 1);
+  g.upd_fused = env_int("PK_UPDATE_FUSED", 1, 0, 1);
   g.pdl_session = env_int("PK_PDL_SESSION", 1, 0, 1);
   g.peer_timeout_ms = env_int("PK_PEER_TIMEOUT_MS", 30000, 1, 3600000);
   g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 2);

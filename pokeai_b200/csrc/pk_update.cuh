@@ -75,6 +75,7 @@ struct PkUpdArgs {
   const uint8_t* terminal;
   const int* a_star;      // [n] online argmax over legal next actions (double DQN), may be null otherwise
   const float* q_target;  // [n][A] target network on next_state
+  const float* v_sel;     // [n] Q_target(s', a*) already selected (fused next-state pass), or null
   int n, A, double_dqn;
   float inv_n, gamma;
 };
@@ -85,7 +86,8 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
                        float* __restrict__ gsum) {
   constexpr int HP = 32 * CPL;
   constexpr int EPT = HP * HP / PK_UPD_THREADS;                                   // hidden-matrix entries per thread
-  constexpr int NS = (PK_N_STATE * HP + PK_UPD_THREADS - 1) / PK_UPD_THREADS;    // state-row entries per thread
+  constexpr int NSG = PK_UPD_THREADS / HP;                                        // row groups (threads per channel)
+  constexpr int NS = ((PK_N_STATE + NSG - 1) / NSG + (NSG <= 8 ? 3 : 0)) & (NSG <= 8 ? ~3 : ~0);  // state rows per thread
   static_assert(EPT >= 1 && HP % EPT == 0, "hidden matrix must split evenly over the CTA");
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -128,7 +130,13 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
   for (int l = 0; l < NL; ++l) acc_b[l] = 0.f;
 #pragma unroll
   for (int i = 0; i < NS; ++i) acc_s[i] = 0.f;
-  const int own_k = (tid * EPT) / HP, own_j0 = (tid * EPT) % HP;
+  // hidden matrices: a thread owns EPT entries.  EPT == 8 (64 channels): a 2 (k) x 4 (j) block, so that one 8-byte load of
+  // h and one 16-byte load of dz feed 8 FMAs (the phase is bound by shared-memory instructions); otherwise one k and EPT
+  // adjacent j.
+  constexpr bool BLK2 = EPT == 8;
+  constexpr int JW = BLK2 ? 4 : EPT;  // adjacent channels per owned k
+  const int own_k = BLK2 ? 2 * (tid / (HP / 4)) : (tid * EPT) / HP;
+  const int own_j0 = BLK2 ? 4 * (tid % (HP / 4)) : (tid * EPT) % HP;
 
   float* T = s_tile + warp * plan.tile_stride;  // this warp's tile record
   uint4* rec = reinterpret_cast<uint4*>(T);
@@ -204,7 +212,9 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
       // ---- TD target (trainer.py:164-184) ----
       float v = 0.f;
       if (!a.terminal[i]) {
-        if (a.double_dqn) {
+        if (a.v_sel != nullptr) {
+          v = a.v_sel[i];
+        } else if (a.double_dqn) {
           v = a.q_target[i * a.A + a.a_star[i]];
         } else {
           const uint4 w1 = __ldg(a.next_state + i * 9 + 1);
@@ -257,31 +267,53 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
       }
 #pragma unroll
       for (int l = 1; l < NL; ++l) {
-        const float hk = Rh[(l - 1) * HP + own_k];
-        const float* dzl = Rdz + l * HP + own_j0;  // EPT adjacent channels: 16-byte loads when EPT allows
-        if constexpr (EPT % 4 == 0) {
+        if constexpr (BLK2) {
+          const float2 h2 = *reinterpret_cast<const float2*>(Rh + (l - 1) * HP + own_k);
+          const float4 d4 = *reinterpret_cast<const float4*>(Rdz + l * HP + own_j0);
+          acc_w[l - 1][0] = fmaf(h2.x, d4.x, acc_w[l - 1][0]);
+          acc_w[l - 1][1] = fmaf(h2.x, d4.y, acc_w[l - 1][1]);
+          acc_w[l - 1][2] = fmaf(h2.x, d4.z, acc_w[l - 1][2]);
+          acc_w[l - 1][3] = fmaf(h2.x, d4.w, acc_w[l - 1][3]);
+          acc_w[l - 1][4] = fmaf(h2.y, d4.x, acc_w[l - 1][4]);
+          acc_w[l - 1][5] = fmaf(h2.y, d4.y, acc_w[l - 1][5]);
+          acc_w[l - 1][6] = fmaf(h2.y, d4.z, acc_w[l - 1][6]);
+          acc_w[l - 1][7] = fmaf(h2.y, d4.w, acc_w[l - 1][7]);
+        } else {
+          const float hk = Rh[(l - 1) * HP + own_k];
+          const float* dzl = Rdz + l * HP + own_j0;  // EPT adjacent channels: 16-byte loads when EPT allows
+          if constexpr (EPT % 4 == 0) {
 #pragma unroll
-          for (int i = 0; i < EPT; i += 4) {
-            const float4 d4 = *reinterpret_cast<const float4*>(dzl + i);
-            acc_w[l - 1][i] = fmaf(hk, d4.x, acc_w[l - 1][i]);
-            acc_w[l - 1][i + 1] = fmaf(hk, d4.y, acc_w[l - 1][i + 1]);
-            acc_w[l - 1][i + 2] = fmaf(hk, d4.z, acc_w[l - 1][i + 2]);
-            acc_w[l - 1][i + 3] = fmaf(hk, d4.w, acc_w[l - 1][i + 3]);
+            for (int i = 0; i < EPT; i += 4) {
+              const float4 d4 = *reinterpret_cast<const float4*>(dzl + i);
+              acc_w[l - 1][i] = fmaf(hk, d4.x, acc_w[l - 1][i]);
+              acc_w[l - 1][i + 1] = fmaf(hk, d4.y, acc_w[l - 1][i + 1]);
+              acc_w[l - 1][i + 2] = fmaf(hk, d4.z, acc_w[l - 1][i + 2]);
+              acc_w[l - 1][i + 3] = fmaf(hk, d4.w, acc_w[l - 1][i + 3]);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < EPT; ++i) acc_w[l - 1][i] = fmaf(hk, dzl[i], acc_w[l - 1][i]);
+          }
+        }
+      }
+      {  // state rows of W0: a thread owns one channel (tid % HP) and NS ADJACENT rows starting at NS * (tid / HP), so the
+         // state values arrive as 16-byte broadcast loads (rows >= 50 are the zero padding of sv and are dropped at the end)
+        static_assert(PK_UPD_THREADS % HP == 0, "state-row ownership assumes HP divides the CTA size");
+        static_assert(NS * (PK_UPD_THREADS / HP) <= 64, "sv is padded to 64 values");
+        const float dzj = Rdz[tid % HP];
+        const float* svk = R + 36 + NS * (tid / HP);
+        if constexpr (NS % 4 == 0) {
+#pragma unroll
+          for (int i = 0; i < NS; i += 4) {
+            const float4 s4 = *reinterpret_cast<const float4*>(svk + i);
+            acc_s[i] = fmaf(s4.x, dzj, acc_s[i]);
+            acc_s[i + 1] = fmaf(s4.y, dzj, acc_s[i + 1]);
+            acc_s[i + 2] = fmaf(s4.z, dzj, acc_s[i + 2]);
+            acc_s[i + 3] = fmaf(s4.w, dzj, acc_s[i + 3]);
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < EPT; ++i) acc_w[l - 1][i] = fmaf(hk, dzl[i], acc_w[l - 1][i]);
-        }
-      }
-      {  // state rows of W0: entry e = tid + 512 i is (row e / HP, channel e % HP); 512 % HP == 0, so the channel -- and
-         // with it the dz operand -- is the same for all of a thread's entries
-        static_assert(PK_UPD_THREADS % HP == 0, "state-row ownership assumes HP divides the CTA size");
-        const float dzj = Rdz[tid % HP];
-        const int k0 = tid / HP;
-#pragma unroll
-        for (int i = 0; i < NS; ++i) {
-          const int k = k0 + (PK_UPD_THREADS / HP) * i;
-          if (k < PK_N_STATE) acc_s[i] = fmaf(R[36 + k], dzj, acc_s[i]);
+          for (int i = 0; i < NS; ++i) acc_s[i] = fmaf(svk[i], dzj, acc_s[i]);
         }
       }
     }
@@ -318,8 +350,8 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
   float* out = partial + (size_t)blockIdx.x * lay.total;
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
-    const int e = tid + PK_UPD_THREADS * i;
-    if (e < PK_N_STATE * HP) out[lay.w1t + e] = acc_s[i];
+    const int k = NS * (tid / HP) + i;
+    if (k < PK_N_STATE) out[lay.w1t + k * HP + (tid % HP)] = acc_s[i];
   }
   for (int e = tid; e < (lay.C - PK_N_STATE) * HP; e += PK_UPD_THREADS)
     out[lay.w1t + PK_N_STATE * HP + e] = SPARSE_SMEM ? s_gacc[e] : 0.f;
@@ -332,7 +364,7 @@ pk_dqn_backward_kernel(PkUpdArgs a, const float* __restrict__ prep, PkLayout lay
 #pragma unroll
   for (int l = 1; l < NL; ++l)
 #pragma unroll
-    for (int i = 0; i < EPT; ++i) out[lay.wl[l] + own_k * HP + own_j0 + i] = acc_w[l - 1][i];
+    for (int i = 0; i < EPT; ++i) out[lay.wl[l] + (own_k + i / JW) * HP + own_j0 + i % JW] = acc_w[l - 1][i];
   if (tid == 0) {  // bout[0] = d/d(output bias), bout[1] = this CTA's share of the loss
     out[lay.bout + 0] = acc_bout;
     out[lay.bout + 1] = acc_loss;
@@ -349,6 +381,38 @@ __global__ void pk_dqn_reduce_kernel(const float* __restrict__ partial, int n_ct
   float s = accumulate ? gsum[p] : 0.f;
   for (int c = 0; c < n_cta; ++c) s += partial[(size_t)c * total + p];
   gsum[p] = s;
+}
+
+// the two kernels above in one launch.  One thread per PREPARED position p (so that the 148 partial vectors are read
+// with coalesced loads: the flat order is the transpose of the prepared one): s = (gsum[p] if accumulate) + sum over
+// CTAs of partial[cta][p], in CTA order (deterministic), written to the flat state_dict-ordered gradient at the
+// parameter p belongs to (padding positions are dropped); the loss shares ride at bout + 1
+__global__ void pk_dqn_reduce_flat_kernel(const float* __restrict__ partial, int n_cta, PkParamLayout P, PkLayout lay,
+                                          const float* __restrict__ gsum, int accumulate, float* __restrict__ grad,
+                                          float* __restrict__ loss) {
+  const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= lay.total) return;
+  const bool is_loss = p == lay.bout + 1;
+  const int i = pk_prepared_to_flat(P, lay, p);
+  if (i < 0 && !is_loss) return;
+  float s0 = (accumulate && !is_loss) ? gsum[p] : 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  const float* src = partial + p;
+  int c = 0;
+  for (; c + 4 <= n_cta; c += 4) {  // four loads in flight; the order of the additions is fixed all the same
+    const float v0 = src[(size_t)c * lay.total], v1 = src[(size_t)(c + 1) * lay.total];
+    const float v2 = src[(size_t)(c + 2) * lay.total], v3 = src[(size_t)(c + 3) * lay.total];
+    s0 += v0;
+    s1 += v1;
+    s2 += v2;
+    s3 += v3;
+  }
+  for (; c < n_cta; ++c) s0 += src[(size_t)c * lay.total];
+  const float s = (s0 + s1) + (s2 + s3);
+  if (is_loss) {
+    if (loss != nullptr) *loss = s;
+  } else {
+    grad[i] = s;
+  }
 }
 
 // prepared-layout sums -> flat state_dict-ordered gradient (+ the loss)

@@ -145,10 +145,27 @@ def _emulated_backward(sd, feat, nl, dq):
     return g
 
 
-@pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 256, 64), (6, 4, 512, 200), (4, 3, 256, 8)])
+def _autocast_grads(sd, feat, dq, nl, H, dev):
+    """what eager PyTorch gives on the same GPU with bf16 autocast (the reference's MLPModel under torch.autocast):
+    the yardstick for how far a bf16 tensor-core backward may be from fp32 autograd"""
+    x = torch.from_numpy(feat).to(dev)
+    params = {k: v.clone().to(dev).requires_grad_(True) for k, v in sd.items()}
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        h = x
+        for i in range(nl):
+            h = torch.relu(torch.nn.functional.conv1d(h, params[f"layers.{i}.weight"], params[f"layers.{i}.bias"]))
+        q = torch.nn.functional.conv1d(h, params["output.weight"], params["output.bias"]).view(x.shape[0], -1)
+    (q.float() * torch.from_numpy(dq).to(dev)).sum().backward()
+    return {k: v.grad.float().cpu() for k, v in params.items()}
+
+
+@pytest.mark.parametrize("ps,nl,H,B", [(6, 2, 256, 64), (6, 4, 512, 200), (4, 3, 256, 8), (6, 4, 2048, 96)])
 def test_wide_backward_matches_oracle(tables, dev, ps, nl, H, B):
-    """flat gradient of sum(dq * q) against (a) the hand-derived bf16-emulating oracle (tight) and (b) torch CPU fp32
-    autograd through the reference forward (bf16 tolerance, relative to each tensor's norm)"""
+    """flat gradient of sum(dq * q) against (a) the hand-derived bf16-emulating oracle (tight), (b) torch CPU fp32
+    autograd through the reference forward, with the error of eager PyTorch under bf16 autocast on the same GPU as the
+    yardstick (a bf16 tensor-core backward cannot be closer to fp32 than bf16 rounding allows; ours must not be
+    materially further than torch's own).  The benchmark's shape, 4 x 2048, is one of the cases; per-tensor errors are
+    written to gpurun_out/ when that directory exists (profiles/r02_wide_grad_errors.json)."""
     from oracle import packed_oracle, ref_port
     from pokeai_b200 import ops, wide
     from pokeai_b200.packed import synth_packed
@@ -179,7 +196,13 @@ def test_wide_backward_matches_oracle(tables, dev, ps, nl, H, B):
         off += n
         scale = float(gem[k].abs().max()) + 1e-12
         err_em = float((gk - gem[k]).abs().max()) / scale
-        assert err_em < 5e-3, f"{k}: {err_em:.2e} of the tensor's max against the bf16-emulating oracle"
+        # the emulation rounds the same values to bf16 but sums in a different order: an activation whose fp32 sum sits
+        # on a rounding boundary flips one bf16 ulp (2^-8 relative), more often the longer the sums (K = 2048)
+        if H <= 512:
+            assert err_em < 5e-3, f"{k}: {err_em:.2e} of the tensor's max against the bf16-emulating oracle"
+        else:  # 2048-long sums: single elements flip by an ulp of bf16 here and there; bound the tensor as a whole
+            fro = float((gk - gem[k]).norm() / (gem[k].norm() + 1e-12))
+            assert fro < 3e-2, f"{k}: Frobenius {fro:.2e} (max {err_em:.2e}) against the emulating oracle"
         ref = params[k].grad
         # bf16 tolerance against fp32 autograd: operands, activations and dZ are rounded to bf16 (2^-9 relative each) and
         # ReLU gates of near-zero pre-activations can flip, so the bound is on the tensor as a whole
@@ -188,6 +211,29 @@ def test_wide_backward_matches_oracle(tables, dev, ps, nl, H, B):
         print(f"{k}: emulated-oracle err {err_em:.2e}, fp32 rel {rel:.3f}, cos {cos:.5f}")
         assert rel < 0.15 and cos > 0.99, f"{k}: relative error {rel:.3f}, cosine {cos:.4f} against fp32 autograd"
     assert off == flat.numel()
+    # (c) the same errors for eager PyTorch with bf16 autocast; ours must stay within 1.3x of it (+ 0.01)
+    gac = _autocast_grads(sd, fo, dq, nl, H, dev)
+    report, off = {}, 0
+    for k, v in sd.items():
+        n = v.numel()
+        gk = flat[off:off + n].reshape(v.shape)
+        off += n
+        ref = params[k].grad
+        rel = float((gk - ref).norm() / (ref.norm() + 1e-12))
+        rel_ac = float((gac[k] - ref).norm() / (ref.norm() + 1e-12))
+        cos = float((gk * ref).sum() / (gk.norm() * ref.norm() + 1e-20))
+        report[k] = {"rel_frobenius_vs_fp32": rel, "cosine_vs_fp32": cos, "torch_autocast_bf16_rel_vs_fp32": rel_ac,
+                     "max_err_vs_bf16_emulating_oracle_over_max": float((gk - gem[k]).abs().max()) /
+                     (float(gem[k].abs().max()) + 1e-12)}
+        assert rel <= 1.3 * rel_ac + 0.01, f"{k}: {rel:.4f} against fp32, torch bf16 autocast gives {rel_ac:.4f}"
+    import json
+    from pathlib import Path
+    out = Path(__file__).resolve().parents[1] / "gpurun_out"
+    if out.is_dir():
+        f = out / "r02_wide_grad_errors.json"
+        cur = json.loads(f.read_text()) if f.exists() else {}
+        cur[f"{nl}x{H} A={A} B={B}"] = report
+        f.write_text(json.dumps(cur, indent=1))
     # bit-reproducible: a second backward gives the same bits
     grad2 = wide.train_backward(prepared, nl, H, B, A, ws, torch.from_numpy(dq).to(dev))
     assert torch.equal(grad, grad2)
