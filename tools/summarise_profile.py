@@ -48,8 +48,9 @@ if rep.exists():
                       r"smsp__inst_executed_op_tma_st.sum$|sm__cycles_elapsed.avg$|"
                       r"smsp__average_warps_issue_stalled_(long_scoreboard|short_scoreboard|wait|barrier|mio_throttle|lg_throttle|math_pipe_throttle|not_selected)_per_issue_active.ratio)")
     with open(P / f"{rnd}_ncu_full_raw.txt", "w") as f:
-        f.write(f"# ncu --set full --clock-control none --import-source on -k regex:pk_decide -s 6 -c 3  python tools/prof_decide.py\n")
-        f.write("# columns: launch 1 = pk_encode (features+mask only), 2 = pk_decide with features, 3 = pk_decide without features; B = 4096\n")
+        f.write(f"# ncu --set full --clock-control none --import-source on -k regex:pk_decide_kernel  python tools/prof_decide.py (last round)\n")
+        f.write("# columns: launch 1 = pk_encode (features+mask only), 2 = pk_decide with features"
+                + (", 3 = pk_decide without features" if len(data) > 2 else "") + "; B = 4096\n")
         for i, h in enumerate(hdr):
             if keep.search(h):
                 f.write(f"{h:90s} {units[i]:16s} " + "  ".join(f"{r[i][:40]:>16s}" for r in data) + "\n")
@@ -57,11 +58,13 @@ if rep.exists():
     hi = {h: i for i, h in enumerate(hdr)}
     tr = [float(r[hi["dram__bytes_read.sum"]].replace(",", "")) * {"Kbyte": 1e3, "Mbyte": 1e6, "byte": 1, "Gbyte": 1e9}[units[hi["dram__bytes_read.sum"]]] for r in data]
     tw = [float(r[hi["dram__bytes_write.sum"]].replace(",", "")) * {"Kbyte": 1e3, "Mbyte": 1e6, "byte": 1, "Gbyte": 1e9}[units[hi["dram__bytes_write.sum"]]] for r in data]
-    traffic = {"pk_decide_kernel@B=4096": tr[1] + tw[1], "pk_encode@B=4096": tr[0] + tw[0], "pk_decide_nofeat@B=4096": tr[2] + tw[2],
+    traffic = {"pk_decide_kernel@B=4096": tr[1] + tw[1], "pk_encode@B=4096": tr[0] + tw[0],
                "note": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, one isolated launch: the 92 MB "
                        "of output of one 4096-state launch fits the 126 MB L2, so part of it is still dirty in L2 when the "
                        "kernel ends and is not counted; the steady-state (rotating buffers) DRAM write traffic is the full 92 MB",
                "source": f"profiles/{rnd}_ncu_full_raw.txt"}
+    if len(data) > 2:
+        traffic["pk_decide_nofeat@B=4096"] = tr[2] + tw[2]
     (P / "traffic.json").write_text(json.dumps(traffic, indent=1) + "\n")
     for which, name in ((1, "decide_feat"),):
         o = subprocess.run([sys.executable, str(ROOT / "tools" / "ncu_lines.py"), str(rep), str(which), "45"],
