@@ -33,7 +33,7 @@ from typing import Iterable, List, Optional, Sequence
 import numpy as np
 
 from .observation import (ActivePokeStatus, BattleStatus, PossibleAction, RLPolicyObservation, RANK_KEYS)
-from .tables import (MAX_ACTIONS, MAX_MOVES, STATUS_CODE, STATUS_FNT, WEATHER_CODE, Tables, load_tables,
+from .tables import (MAX_ACTIONS, MAX_MOVES, N_STATE, STATUS_CODE, STATUS_FNT, WEATHER_CODE, Tables, load_tables,
                      NV_CONDITIONS, WEATHERS)
 
 PK_ACT_DTYPE = np.dtype([("flags", "u1"), ("species", "u1"), ("item", "u1"), ("n_moves", "u1"),
@@ -154,6 +154,77 @@ def unpack_observation(rec, tables: Optional[Tables] = None) -> RLPolicyObservat
         acts.append(PossibleAction(key, tables.species_ids[int(ar["species"])], None if sw else moves[0], sw,
                                    bool(ar["flags"] & FLAG_FORCE), moves, tables.items[int(ar["item"])]))
     return RLPolicyObservation(bs, {}, acts)
+
+
+# --------------------------------------------------------------------------------------
+# dense (C, A) features -> packed record (reference `resume=True` replay buffers)
+# --------------------------------------------------------------------------------------
+def _ratio_pair(r: np.float32, max_den: int):
+    """Smallest (num, den), 1 <= den <= max_den, 0 <= num <= den, with float32(num / den) == r: the encoder only ever
+    sees the ratio (state_feature_extractor.py:122,150), so any such pair encodes to the same bits."""
+    den = np.arange(1, max_den + 1, dtype=np.int64)
+    num = np.rint(np.float64(r) * den).astype(np.int64)
+    ok = ((num / den).astype(np.float32) == np.float32(r)) & (num >= 0) & (num <= den)
+    hit = np.flatnonzero(ok)
+    if hit.size == 0:
+        raise ValueError(f"{float(r)!r} is not a ratio of two integers with a denominator <= {max_den}")
+    return int(num[hit[0]]), int(den[hit[0]])
+
+
+def record_from_dense(feat: np.ndarray, mask: np.ndarray, tables: Optional[Tables] = None) -> np.ndarray:
+    """Invert FeatureExtractor.transform (feature_extractor.py:40-52): a dense (C, A) float32 feature array and its
+    (A,) mask -> a packed record that ENCODES TO THE SAME BITS.  What a reference checkpoint written with
+    `save_state(resume=True)` keeps in its replay buffer (replay_buffer.py:7-15) is exactly such arrays.  One-hot blocks
+    invert exactly; ratios are recovered as the smallest integer pair with the same float32 quotient; the opponent's
+    species is any species with the same type set (only its types are encoded, state_feature_extractor.py:125-138).
+    Raises ValueError for arrays that are not the image of an observation."""
+    tables = tables or load_tables()
+    feat = np.asarray(feat, dtype=np.float32)
+    mask = np.asarray(mask)
+    C, A = feat.shape
+    if C != tables.n_channels or A > MAX_ACTIONS or mask.shape != (A,):
+        raise ValueError(f"expected ({tables.n_channels}, A <= {MAX_ACTIONS}) features and an (A,) mask")
+    rec = np.zeros(1, dtype=PK_OBS_DTYPE)[0]
+    sv = feat[:N_STATE, 0]
+    for i in range(2):
+        rec["remaining"][i], rec["total"][i] = _ratio_pair(sv[i], 255)
+        rec["hp_cur"][i], rec["hp_max"][i] = _ratio_pair(sv[19 + i], 65535)
+        st = np.flatnonzero(sv[21 + 6 * i:27 + 6 * i])
+        if st.size > 1:
+            raise ValueError("more than one non-volatile status set")
+        rec["status"][i] = 0 if st.size == 0 else int(st[0]) + 1
+        for k in range(7):
+            v = sv[33 + 7 * i + k]
+            rank = int(round(float(v) * 12.0 - 6.0))
+            if not -6 <= rank <= 6 or np.float32((rank + 6) / 12) != v:
+                raise ValueError(f"{float(v)!r} is not a rank feature")
+            rec["boost"][i][k] = rank
+    tmask = np.uint32(sum(1 << t for t in np.flatnonzero(sv[2:19])))
+    cand = np.flatnonzero(tables.species_type_mask == tmask)
+    if cand.size == 0:
+        raise ValueError("no species has the opponent's type set")
+    rec["opp_species"] = int(cand[0])
+    w = np.flatnonzero(sv[47:50])
+    if w.size > 1:
+        raise ValueError("more than one weather set")
+    rec["weather"] = 0 if w.size == 0 else int(w[0]) + 1
+    n_act = int(mask.sum())
+    if not (np.all(mask[:n_act] == 1) and np.all(mask[n_act:] == 0)):
+        raise ValueError("the action mask is not a prefix mask")
+    rec["n_act"] = n_act
+    ch = feat[N_STATE:]
+    for c in range(n_act):
+        col = ch[:, c]
+        sp = np.flatnonzero(col[tables.CH_SPECIES:tables.CH_MOVE])
+        mv = np.flatnonzero(col[tables.CH_MOVE:tables.CH_ITEM])
+        it = np.flatnonzero(col[tables.CH_ITEM:])
+        if sp.size != 1 or it.size != 1 or not 1 <= mv.size <= MAX_MOVES:
+            raise ValueError(f"action column {c} is not the image of a PossibleAction")
+        ar = rec["act"][c]
+        ar["flags"] = (FLAG_SWITCH if col[tables.CH_SWITCH] != 0 else 0) | (FLAG_FORCE if col[tables.CH_FORCE] != 0 else 0)
+        ar["species"], ar["item"], ar["n_moves"] = int(sp[0]), int(it[0]), int(mv.size)
+        ar["move"][:mv.size] = mv
+    return rec
 
 
 # --------------------------------------------------------------------------------------

@@ -31,11 +31,27 @@ class ReplayBufferItem(NamedTuple):
     reward: float
 
 
-def _as_record(x) -> np.ndarray:
+def _as_record(x, mask=None) -> np.ndarray:
+    """A packed record as it is; a dense (C, A) float32 feature array -- what the reference's replay buffer holds
+    (replay_buffer.py:7-15, e.g. in a `resume=True` checkpoint) -- converted to a record that encodes to the same bits."""
     if isinstance(x, (np.ndarray, np.void)) and x.dtype == PK_OBS_DTYPE:
         return x
-    raise TypeError("pokeai_b200 replay items hold packed observation records (PK_OBS_DTYPE); dense (C, A) feature "
-                    "arrays from a reference checkpoint cannot be converted back to observations")
+    if isinstance(x, np.ndarray) and x.ndim == 2 and mask is not None:
+        from .packed import record_from_dense
+        return record_from_dense(x, mask)
+    raise TypeError("replay items hold packed observation records (PK_OBS_DTYPE) or dense (C, A) feature arrays with "
+                    "their action mask")
+
+
+def from_reference(buffer) -> "ReplayBuffer":
+    """A reference ReplayBuffer (deque of dense items, replay_buffer.py:18-32) -> the packed ring."""
+    if isinstance(buffer, ReplayBuffer):
+        return buffer
+    items = list(buffer.buffer)
+    out = ReplayBuffer(getattr(buffer.buffer, "maxlen", None))
+    for it in items:
+        out.append(it)
+    return out
 
 
 class _BufferView:
@@ -98,12 +114,12 @@ class ReplayBuffer:
         if self.maxlen == 0:
             return
         p = self._slot_for_append()
-        self._state[p] = _as_record(item.state)
+        self._state[p] = _as_record(item.state, item.action_mask)
         if item.next_state is None:
             self._next[p] = np.zeros((), dtype=PK_OBS_DTYPE)
             self._terminal[p] = 1
         else:
-            self._next[p] = _as_record(item.next_state)
+            self._next[p] = _as_record(item.next_state, item.next_action_mask)
             self._terminal[p] = 0
         self._action[p] = item.action
         self._reward[p] = item.reward

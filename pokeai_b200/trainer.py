@@ -239,7 +239,10 @@ class Trainer:
                 ops.prepare_from_flat(trainer._flat_target, trainer._nl, trainer._H, trainer._C,
                                       out=trainer._prepared_target)
             trainer.optimizer.load_state_dict(state["optimizer"])
-            trainer.replay_buffer = state["replay_buffer"]
+            # a checkpoint written by the reference holds ITS ReplayBuffer (dense (617, A) arrays): converted to packed
+            # records that encode to the same bits (packed.record_from_dense)
+            from .replay_buffer import from_reference
+            trainer.replay_buffer = from_reference(state["replay_buffer"])
             trainer.update_loss_history = state["update_loss_history"]
         return trainer
 

@@ -288,6 +288,42 @@ def test_trainer_model_follows_in_place_updates(tables, nl, H):
     check()
 
 
+def test_resume_from_a_reference_style_checkpoint_with_dense_replay(synth_golden, tables):
+    """trainer.py:73-117: a `resume=True` state whose replay buffer is the reference's (a deque of dense (617, A) items)
+    loads: the items are converted to packed records that encode to the same bits, and training goes on"""
+    from collections import deque, namedtuple
+    from oracle import packed_oracle
+    from pokeai_b200.trainer import Trainer
+    rec, ps, feat, mask = synth_golden["ragged6"]
+    Item = namedtuple("ReplayBufferItem", "state action_mask action next_state next_action_mask reward")
+
+    class RefReplay:  # replay_buffer.py:18-32
+        def __init__(self, n):
+            self.buffer = deque(maxlen=n)
+
+    torch.manual_seed(4)
+    random.seed(4)
+    tr = Trainer({"n_layers": 2, "n_channels": 64}, {"batch_size": 16, "first_update_steps": 0, "replay_buffer_size": 500},
+                 {"party_size": 6})
+    state = tr.save_state(resume=True)
+    ref_rb = RefReplay(500)
+    for i in range(0, 120, 2):
+        n_act = int(mask[i].sum())
+        last = i % 20 == 18
+        ref_rb.buffer.append(Item(feat[i], mask[i], i % max(n_act, 1), None if last else feat[i + 1],
+                                  None if last else mask[i + 1], float(i % 3) - 1.0))
+    state["replay_buffer"] = ref_rb
+    tr2 = Trainer.load_state(state, resume=True)
+    assert len(tr2.replay_buffer) == 60 and tr2.replay_buffer.maxlen == 500
+    s, nx, act, rew, term = tr2.replay_buffer.gather(np.arange(60))
+    fs, ms = packed_oracle.encode(s, ps, tables)
+    assert np.array_equal(fs.view(np.uint32), feat[0:120:2].view(np.uint32)) and np.array_equal(ms, mask[0:120:2])
+    before = tr2._flat.clone()
+    tr2._update()
+    assert len(tr2.update_loss_history) == 1 and np.isfinite(tr2.update_loss_history[0])
+    assert not torch.equal(before, tr2._flat)
+
+
 def test_trainer_schedule_checkpoint_and_agents(tables):
     from pokeai_b200.trainer import Trainer, DQN_DEFAULT_PARAMS
     assert DQN_DEFAULT_PARAMS["batch_size"] == 32 and DQN_DEFAULT_PARAMS["target_update"] == 100

@@ -126,3 +126,48 @@ def test_select_restatements():
     assert all(mask[b, s[b]] == 1 for b in range(64))
     np.testing.assert_allclose(p.sum(1), 1.0, rtol=1e-5)
     assert (p[mask == 0] == 0).all()
+
+
+@pytest.mark.parametrize("name", ["full6", "ragged6", "ragged3", "ragged1", "full4"])
+def test_dense_features_invert_to_equivalent_records(synth_golden, tables, name):
+    """reference `resume=True` replay buffers hold dense (617, A) arrays: record_from_dense must give records that
+    encode back to the same bits (the reference's own FeatureExtractor outputs are the input here)"""
+    from oracle import packed_oracle
+    from pokeai_b200.packed import PK_OBS_DTYPE, record_from_dense
+    rec, ps, feat, mask = synth_golden[name]
+    out = np.zeros(len(feat), dtype=PK_OBS_DTYPE)
+    for i in range(len(feat)):
+        out[i] = record_from_dense(feat[i], mask[i], tables)
+    f2, m2 = packed_oracle.encode(out, ps, tables)
+    assert np.array_equal(bits(f2), bits(feat)) and np.array_equal(m2, mask)
+    with pytest.raises(ValueError):
+        bad = feat[0].copy()
+        bad[19, :] = 1.5  # hp_current > hp_max: not the image of an observation
+        record_from_dense(bad, mask[0], tables)
+
+
+def test_replay_buffer_accepts_reference_items(synth_golden, tables):
+    """a reference ReplayBuffer (deque of dense ReplayBufferItem) converts into the packed ring"""
+    from collections import deque, namedtuple
+    from oracle import packed_oracle
+    from pokeai_b200.replay_buffer import from_reference
+    rec, ps, feat, mask = synth_golden["ragged6"]
+    Item = namedtuple("ReplayBufferItem", "state action_mask action next_state next_action_mask reward")
+
+    class RefBuffer:  # replay_buffer.py:18-32
+        def __init__(self):
+            self.buffer = deque(maxlen=1000)
+
+    rb = RefBuffer()
+    for i in range(0, 40, 2):
+        last = i % 8 == 6
+        rb.buffer.append(Item(feat[i], mask[i], i % 4, None if last else feat[i + 1], None if last else mask[i + 1], 0.5 * i))
+    ours = from_reference(rb)
+    assert len(ours) == 20 and ours.maxlen == 1000
+    s, nx, act, rew, term = ours.gather(np.arange(20))
+    fs, ms = packed_oracle.encode(s, ps, tables)
+    assert np.array_equal(bits(fs), bits(feat[0:40:2])) and np.array_equal(ms, mask[0:40:2])
+    keep = term == 0
+    fn, mn = packed_oracle.encode(nx[keep], ps, tables)
+    assert np.array_equal(bits(fn), bits(feat[1:40:2][keep])) and int(term.sum()) == 5
+    assert list(act) == [i % 4 for i in range(0, 40, 2)] and rew[3] == 3.0
