@@ -161,6 +161,40 @@ def leg_update(ctx, NG=32768, nl=2, H=64, steps=20):
             dist.all_reduce(rt.grad, op=dist.ReduceOp.SUM)
         ops.clamp_adam(rt.flat, rt.grad, rt.m, rt.v, nl, H, rt.step_no, lr=lr, betas=betas, eps=eps, prepared=rt.prep)
 
+    # graph-replayable route: the whole step (control-block advance, next-state pass, backward, reduce, [peer exchange +]
+    # clamp + Adam) captured once per gradient-buffer parity and replayed -- no launch arguments change between steps
+    class GraphRoute(Route):
+        def __init__(self, nmax):
+            super().__init__("graph", nmax)
+            self.ctl = ops.make_update_ctl(dev, lr, betas, eps)
+            self.graphs = {}
+
+        def capture(self, batches):
+            """batches[p]: the (fixed) input set the graph of parity p reads"""
+            side = torch.cuda.Stream(device=dev)
+            for p in (1, 0):
+                s, s2, ac, r, t = batches[p]
+
+                def body():
+                    ops.update_ctl_advance(self.ctl)
+                    if px is not None:
+                        gslot, lslot = px.slot(p)
+                        ops.dqn_grad(self.prep, prep_t, nl, H, A, s, s2, ac, r, t, gamma, True, n_global=NG, scratch=self.scratch,
+                                     out_grad=gslot, out_loss=lslot)
+                        px.reduce_clamp_adam_ctl(p, self.flat, self.m, self.v, nl, H, Cn, self.ctl, prepared=self.prep)
+                    else:
+                        ops.dqn_grad(self.prep, prep_t, nl, H, A, s, s2, ac, r, t, gamma, True, n_global=NG, scratch=self.scratch,
+                                     out_grad=self.grad, out_loss=self.loss)
+                        ops.clamp_adam_ctl(self.flat, self.grad, self.m, self.v, nl, H, self.ctl, prepared=self.prep)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    body()
+                self.graphs[p] = g
+
+        def step(self):
+            self.step_no += 1
+            self.graphs[self.step_no & 1].replay()
+
     out = []
     base = {"config": f"configs[3] DQN minibatch update, {NG} packed transitions per step (global), default MLP {nl}x{H}, "
                       f"Double DQN, 5% terminal; dp{world}: contiguous shards of one global minibatch",
@@ -169,6 +203,18 @@ def leg_update(ctx, NG=32768, nl=2, H=64, steps=20):
         rt = Route("single", n)
         ms = _timed(ctx, lambda i: step(rt, sets[i % n_rot], NG), steps)
         out.append(dict(base, exchange="none", transitions_per_s=NG / (ms * 1e-3), ms_per_step=ms, steps=steps))
+        # the same step as a replayed CUDA graph, checked against three plain steps from the same weights first
+        ref, gr = Route("single", n), GraphRoute(n)
+        gr.capture({1: sets[0], 0: sets[1]})
+        for k in range(3):
+            step(ref, sets[k % 2], NG)
+            gr.step()
+        torch.cuda.synchronize()
+        diff = float((ref.flat - gr.flat).abs().max())
+        ms = _timed(ctx, lambda i: gr.step(), steps)
+        out.append(dict(base, exchange="none; the step replayed as one CUDA graph (device-side Adam step count)",
+                        transitions_per_s=NG / (ms * 1e-3), ms_per_step=ms, steps=steps, parity_ok=bool(diff <= 1e-7),
+                        parity={"graph_vs_plain_max_abs": diff}))
         return out
     # ---- parity first: both routes and the single-GPU full-batch update, three steps from the same weights -------
     routes = {"nccl": Route("nccl", n), "full": Route("full", NG)}
@@ -209,6 +255,43 @@ def leg_update(ctx, NG=32768, nl=2, H=64, steps=20):
                                         "nccl: one sum-allreduce of the flat gradient, then pk_clamp_adam"),
                         transitions_per_s=NG / (ms * 1e-3), ms_per_step=ms, steps=steps, parity_ok=parity_ok,
                         parity=checks, ranks=world))
+    if px is not None:
+        # the peer route replayed as CUDA graphs (one per buffer parity): epoch and Adam step advance on the device.
+        # Continues the peer exchange's epochs: the control block starts at the epoch the plain route has reached.
+        peer = routes["peer"]
+        gr = GraphRoute(n)
+        gr.flat.copy_(peer.flat)
+        gr.m.copy_(peer.m)
+        gr.v.copy_(peer.v)
+        gr.prep.copy_(peer.prep)
+        gr.ctl = ops.make_update_ctl(dev, lr, betas, eps, step=peer.step_no, epoch=px.epoch)
+        gr.step_no = px.epoch  # parity of the next epoch selects the graph
+        ref = Route("nccl", n)
+        for t_, s_ in ((ref.flat, peer.flat), (ref.m, peer.m), (ref.v, peer.v), (ref.prep, peer.prep)):
+            t_.copy_(s_)
+        ref.step_no = peer.step_no
+        nxt = (px.epoch + 1) & 1  # parity of the first graph step
+        gr.capture({nxt: sets[0], nxt ^ 1: sets[1]})
+        for k in range(4):
+            step(ref, sets[k % 2], NG)
+            gr.step()
+        px.epoch += 4
+        torch.cuda.synchronize()
+        allp = [torch.empty_like(gr.flat) for _ in range(world)]
+        dist.all_gather(allp, gr.flat)
+        gchecks = {"graph_bit_identical_across_ranks": bool(all(torch.equal(allp[0], p) for p in allp)),
+                   "graph_vs_nccl_max_abs": float((gr.flat - ref.flat).abs().max()),
+                   "peer_timeout_flag": float(px.loss_status[1])}
+        gok = gchecks["graph_bit_identical_across_ranks"] and gchecks["graph_vs_nccl_max_abs"] <= 1e-6 and \
+            gchecks["peer_timeout_flag"] == 0.0
+        okt = torch.tensor([1 if gok else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        ms = _timed(ctx, lambda i: gr.step(), steps + (steps & 1), warm=4)  # whole graph pairs
+        px.epoch += steps + (steps & 1) + 4
+        out.append(dict(base, exchange="peer, the step replayed as CUDA graphs (one per buffer parity; epoch and Adam step "
+                                       "advance on the device: pk_update_ctl)",
+                        transitions_per_s=NG / (ms * 1e-3), ms_per_step=ms, steps=steps + (steps & 1),
+                        parity_ok=bool(int(okt.item()) == 1), parity=gchecks, ranks=world))
     return out
 
 

@@ -235,6 +235,22 @@ PK_API int pk_clamp_adam(float* params, const float* grad, float* exp_avg, float
                   int n_channels, int in_channels, float lr, float beta1, float beta2, float eps, int step,
                   float* prepared, void* stream);
 
+/* Graph-replayable form of the optimiser step.  A captured CUDA graph freezes launch arguments, and two of them change
+ * every step: Adam's step count (bias corrections) and the epoch of the peer exchange.  With a control block in DEVICE
+ * memory they advance on the device instead: capture [pk_update_ctl_advance, pk_dqn_grad, pk_clamp_adam_ctl or
+ * pk_peer_clamp_adam_ctl] once (for the peer route: once per gradient-buffer parity, replayed alternately) and replay.
+ * Initialise {epoch = 0, step = 0, lr, beta1, beta2, eps} with a copy from the host; same arithmetic as pk_clamp_adam
+ * (the bias corrections are computed in double, by one thread per block). */
+typedef struct pk_update_ctl {
+  uint32_t epoch; /* peer exchange epoch of the step being taken (after pk_update_ctl_advance: 1, 2, 3, ...) */
+  int32_t step;   /* Adam step count of the step being taken (1-based) */
+  float lr, beta1, beta2, eps;
+  uint32_t reserved[2];
+} pk_update_ctl;
+PK_API int pk_update_ctl_advance(pk_update_ctl* ctl_dev, void* stream); /* epoch += 1, step += 1 */
+PK_API int pk_clamp_adam_ctl(float* params, const float* grad, float* exp_avg, float* exp_avg_sq, int n_layers,
+                      int n_channels, int in_channels, const pk_update_ctl* ctl_dev, float* prepared, void* stream);
+
 /* Data-parallel form of pk_clamp_adam: gradient sum over ranks + clamp + Adam in ONE kernel over NVLink peer memory
  * (replaces dist.all_reduce(grad) + the clamp / optimizer.step of trainer.py:193-195 at world size > 1).
  * peer_grads[r] (r < world): device pointer, valid in THIS process, to rank r's gradient buffer for this epoch:
@@ -253,6 +269,12 @@ PK_API int pk_peer_clamp_adam(float* params, const float* const* peer_grads, uin
                        int world, uint32_t epoch, float* exp_avg, float* exp_avg_sq, int n_layers, int n_channels,
                        int in_channels, float lr, float beta1, float beta2, float eps, int step, float* prepared,
                        float* grad_sum, float* loss_status, void* stream);
+/* The same with epoch, step and the Adam constants read from a device control block (see pk_update_ctl): peer_grads
+ * must be the buffer set of the parity of the epoch the graph will run at. */
+PK_API int pk_peer_clamp_adam_ctl(float* params, const float* const* peer_grads, uint32_t* const* peer_flags, int rank,
+                           int world, const pk_update_ctl* ctl_dev, float* exp_avg, float* exp_avg_sq, int n_layers,
+                           int n_channels, int in_channels, float* prepared, float* grad_sum, float* loss_status,
+                           void* stream);
 
 /* ---- host-buffer session (for non-torch callers, and the end-to-end measurement) ------
  * Owns device buffers for up to max_batch observations and one stream.  *_host calls copy

@@ -429,6 +429,24 @@ __global__ void pk_dqn_flat_kernel(const float* __restrict__ gsum, PkParamLayout
 struct PkAdam {
   float one_minus_b1, b2, one_minus_b2, step_size, bc2_sqrt, eps;
 };
+// The same factors from the device-resident control block (pk_update_ctl, include/pokeai_b200.h) instead of launch
+// arguments, so that a captured CUDA graph of the update step can be replayed: epoch and step advance on the device.
+// torch/optim/adam.py computes the bias corrections in double on the host; thread 0 of every block does the same here.
+__device__ __forceinline__ void pk_adam_from_ctl(const pk_update_ctl* ctl, PkAdam* h, unsigned* epoch) {
+  const double b1 = (double)ctl->beta1, b2 = (double)ctl->beta2;
+  const double bc1 = 1.0 - pow(b1, (double)ctl->step), bc2 = 1.0 - pow(b2, (double)ctl->step);
+  h->one_minus_b1 = (float)(1.0 - b1);
+  h->b2 = ctl->beta2;
+  h->one_minus_b2 = (float)(1.0 - b2);
+  h->step_size = (float)((double)ctl->lr / bc1);
+  h->bc2_sqrt = (float)sqrt(bc2);
+  h->eps = ctl->eps;
+  *epoch = ctl->epoch;
+}
+__global__ void pk_update_ctl_advance_kernel(pk_update_ctl* ctl) {
+  ctl->epoch += 1u;
+  ctl->step += 1;
+}
 // ---- gradient exchange over NVLink peer memory, fused with clamp + Adam ----------------------------------------------
 // The data-parallel update has one exchange: the sum over ranks of the flat gradient, followed by the
 // clamp and the Adam step on every rank.  NCCL does it as allreduce -> separate kernel; for the default network the
@@ -466,7 +484,15 @@ __device__ __forceinline__ float pk_ld_relaxed_sys(const float* p) {
 __global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe, float* __restrict__ m,
                                           float* __restrict__ v, PkParamLayout P, PkLayout lay, PkAdam h,
                                           float* __restrict__ prepared, float* __restrict__ grad_sum,
-                                          float* __restrict__ loss_status) {
+                                          float* __restrict__ loss_status, const pk_update_ctl* __restrict__ ctl) {
+  if (ctl != nullptr) {  // graph-replayable form: epoch and Adam factors come from device memory
+    __shared__ PkAdam s_h;
+    __shared__ unsigned s_epoch;
+    if (threadIdx.x == 0) pk_adam_from_ctl(ctl, &s_h, &s_epoch);
+    __syncthreads();
+    h = s_h;
+    pe.epoch = s_epoch;
+  }
   if (blockIdx.x == 0 && threadIdx.x < pe.world) {  // publish: this rank's gradient was written by earlier kernels
     __threadfence_system();
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pe.flags[threadIdx.x] + pe.rank), "r"(pe.epoch) : "memory");
@@ -524,7 +550,14 @@ __global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe
 
 __global__ void pk_clamp_adam_kernel(float* __restrict__ params, const float* __restrict__ grad, float* __restrict__ m,
                                      float* __restrict__ v, PkParamLayout P, PkLayout lay, PkAdam h,
-                                     float* __restrict__ prepared) {
+                                     float* __restrict__ prepared, const pk_update_ctl* __restrict__ ctl) {
+  if (ctl != nullptr) {
+    __shared__ PkAdam s_h;
+    __shared__ unsigned s_epoch;
+    if (threadIdx.x == 0) pk_adam_from_ctl(ctl, &s_h, &s_epoch);
+    __syncthreads();
+    h = s_h;
+  }
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P.total) return;
   const float g = fminf(fmaxf(grad[i], -1.0f), 1.0f);            // trainer.py:193-194

@@ -121,3 +121,24 @@ class PeerGradExchange:
             float(betas[0]), float(betas[1]), float(eps), int(step),
             prepared.data_ptr() if prepared is not None else None,
             grad_sum.data_ptr() if grad_sum is not None else None, self.loss_status.data_ptr(), stream))
+
+    # ---- graph-replayable form (pk_update_ctl) ------------------------------------------------------------------
+    def slot(self, parity: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        """(gradient, loss share) views of this rank's buffer of the given epoch parity (fixed addresses: what a
+        captured graph of the step writes into)."""
+        o = self.FLAG_FLOATS + (parity & 1) * self.npad
+        return self.buf[o:o + self.n], self.buf[o + self.n:o + self.n + 1]
+
+    def reduce_clamp_adam_ctl(self, parity: int, params: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor,
+                              n_layers: int, n_channels: int, in_channels: int, ctl: torch.Tensor,
+                              prepared: Optional[torch.Tensor] = None, grad_sum: Optional[torch.Tensor] = None) -> None:
+        """`reduce_clamp_adam` with epoch, step and the Adam constants read from the device control block: capture
+        [ops.update_ctl_advance(ctl), ops.dqn_grad(..., out_grad / out_loss = slot(p)), this] once per parity p and
+        replay the two graphs alternately, parity 1 first (the epoch counts from 1)."""
+        from . import _native as N
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(N.lib().pk_peer_clamp_adam_ctl(
+            params.data_ptr(), self._grad_ptrs[parity & 1], self._flag_ptrs, self.rank, self.world, ctl.data_ptr(),
+            exp_avg.data_ptr(), exp_avg_sq.data_ptr(), int(n_layers), int(n_channels), int(in_channels),
+            prepared.data_ptr() if prepared is not None else None,
+            grad_sum.data_ptr() if grad_sum is not None else None, self.loss_status.data_ptr(), stream))

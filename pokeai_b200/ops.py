@@ -216,6 +216,30 @@ def clamp_adam(params: torch.Tensor, grad: torch.Tensor, exp_avg: torch.Tensor, 
                                   _stream_ptr(dev)))
 
 
+def make_update_ctl(device, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, step: int = 0, epoch: int = 0):
+    """A device-resident pk_update_ctl (include/pokeai_b200.h): what lets a captured CUDA graph of the update step be
+    replayed -- Adam's step count and the peer-exchange epoch advance on the device (`update_ctl_advance`)."""
+    host = np.zeros(8, dtype=np.uint32)
+    host[0], host[1] = epoch, np.int32(step).view(np.uint32)
+    host[2:6] = np.array([lr, betas[0], betas[1], eps], dtype=np.float32).view(np.uint32)
+    return torch.from_numpy(host.view(np.int32)).to(device)
+
+
+def update_ctl_advance(ctl: torch.Tensor) -> None:
+    N.check(N.lib().pk_update_ctl_advance(ctl.data_ptr(), _stream_ptr(_dev(ctl))))
+
+
+def clamp_adam_ctl(params: torch.Tensor, grad: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor,
+                   n_layers: int, n_channels_: int, ctl: torch.Tensor, prepared: Optional[torch.Tensor] = None) -> None:
+    """`clamp_adam` with the step count and the Adam constants read from the device control block `ctl`."""
+    dev = _dev(params)
+    for t in (params, grad, exp_avg, exp_avg_sq):
+        assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == params.numel()
+    N.check(N.lib().pk_clamp_adam_ctl(params.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+                                      n_layers, n_channels_, n_channels(), ctl.data_ptr(),
+                                      prepared.data_ptr() if prepared is not None else None, _stream_ptr(dev)))
+
+
 def unflatten(flat: torch.Tensor, n_layers: int, H: int, Cin: int) -> dict:
     """Flat parameter / gradient vector -> dict with the reference's state_dict keys and shapes."""
     out, off = {}, 0

@@ -288,6 +288,57 @@ def test_trainer_model_follows_in_place_updates(tables, nl, H):
     check()
 
 
+def test_update_step_replayed_as_cuda_graph(tables):
+    """pk_update_ctl: Adam's step count lives in device memory, so a captured graph of the whole update step
+    (advance, next-state pass, backward, reduce, clamp + Adam) can be replayed; same bits as the plain calls"""
+    from oracle import ref_port
+    from pokeai_b200 import ops
+    from pokeai_b200.packed import synth_packed
+    dev = torch.device("cuda:0")
+    nl, H, A, n = 2, 64, 9, 1024
+    sd = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=1)
+    sd_t = ref_port.init_mlp_params(tables.n_channels, nl, H, seed=2)
+    prep_t = ops.prepare_weights(sd_t, dev)[0]
+    rng = np.random.default_rng(0)
+    sets = []
+    for i in range(2):
+        s = synth_packed(n, seed=20 + i, party_size=6, kind="ragged", tables=tables)
+        s2 = synth_packed(n, seed=40 + i, party_size=6, kind="ragged", tables=tables)
+        sets.append((ops.packed_to_device(s, dev), ops.packed_to_device(s2, dev),
+                     torch.from_numpy((rng.random(n) * s["n_act"]).astype(np.int32)).to(dev),
+                     torch.from_numpy(rng.uniform(-1, 1, n).astype(np.float32)).to(dev),
+                     torch.from_numpy((rng.random(n) < 0.05).astype(np.uint8)).to(dev)))
+
+    def fresh():
+        prep, _, _, flat = ops.prepare_weights(sd, dev)
+        return prep, flat, torch.zeros_like(flat), torch.zeros_like(flat)
+
+    # plain: launch arguments carry the step count
+    prep_a, flat_a, ma, va = fresh()
+    for k in range(1, 6):
+        g, _ = ops.dqn_grad(prep_a, prep_t, nl, H, A, *sets[k % 2], gamma=0.95)
+        ops.clamp_adam(flat_a, g, ma, va, nl, H, k, lr=1e-2, prepared=prep_a)
+    # graphs: one per input set, the step count advances on the device
+    prep_b, flat_b, mb, vb = fresh()
+    ctl = ops.make_update_ctl(dev, lr=1e-2)
+    grad, loss = torch.empty_like(flat_b), torch.zeros(1, device=dev)
+    graphs = {}
+    side = torch.cuda.Stream(device=dev)
+    for p in (0, 1):
+        gph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gph, stream=side):
+            ops.update_ctl_advance(ctl)
+            ops.dqn_grad(prep_b, prep_t, nl, H, A, *sets[p], gamma=0.95, out_grad=grad, out_loss=loss)
+            ops.clamp_adam_ctl(flat_b, grad, mb, vb, nl, H, ctl, prepared=prep_b)
+        graphs[p] = gph
+    for k in range(1, 6):
+        graphs[k % 2].replay()
+    torch.cuda.synchronize()
+    assert int(ctl.cpu()[1]) == 5  # the device-side step count
+    assert float((flat_a - flat_b).abs().max()) <= 1e-7
+    assert torch.equal(ops.prepare_from_flat(flat_b, nl, H, tables.n_channels), prep_b)
+
+
 def test_resume_from_a_reference_style_checkpoint_with_dense_replay(synth_golden, tables):
     """trainer.py:73-117: a `resume=True` state whose replay buffer is the reference's (a deque of dense (617, A) items)
     loads: the items are converted to packed records that encode to the same bits, and training goes on"""

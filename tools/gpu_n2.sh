@@ -1,17 +1,17 @@
 #!/bin/bash
-# two-GPU checks: the 2-GPU pytest cases and bench.py at N = 2 (secondary legs: both exchange routes + parity_ok)
 set -u
 OUT=gpurun_out
 mkdir -p $OUT
-echo "== pytest (2 GPUs visible)"; timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest_n2_r02.log 2>&1; echo "rc=$?"; tail -4 $OUT/pytest_n2_r02.log
-echo "== bench N=2"
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 20 --warmup 5 > $OUT/bench_n2_r02.json 2> $OUT/bench_n2_r02.err
-echo "rc=$?"; tail -3 $OUT/bench_n2_r02.err
+for N in 1 2; do
+echo "== bench N=$N (update leg only)"
+if [ $N -eq 1 ]; then timeout 600 python bench.py --steps 5 --warmup 3 --cpu-seconds 0 --no-e2e --skip-legs shard65536,wide,wide_update,gpu_reference,concurrent64 > $OUT/b.json 2> $OUT/b.err
+else timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2952$N bench.py --gpus $N --steps 5 --warmup 3 --no-e2e --skip-legs shard65536,wide,wide_update,gpu_reference,concurrent64 > $OUT/b.json 2> $OUT/b.err; fi
+echo "rc=$?"; tail -3 $OUT/b.err
 python - <<'PY'
 import json
-d=json.loads(open('gpurun_out/bench_n2_r02.json').read().strip().splitlines()[-1])
-print({k:d[k] for k in ('value','ms_per_step','gpu_launches','n_gpus')}, d['roofline']['frac'], d['roofline']['launch_us'])
-print('e2e', d['e2e']['value'])
+d=json.loads(open('gpurun_out/b.json').read().strip().splitlines()[-1])
 for r in d['roofline']['secondary'] or []:
-    print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k not in ('config',)}, '|', r.get('config','')[:60])
+    print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','exchange','transitions_per_s','ms_per_step','parity_ok','parity','error')})
 PY
+done
+echo "== pytest update"; timeout 900 python -m pytest tests/test_gpu_update.py -m gpu -x -q 2>&1 | tail -3
