@@ -9,7 +9,7 @@
 //                           the reference is never built
 //   pk_wide_gemm_kernel     Y = act(X W^T + b): TMA (cp.async.bulk.tensor, SWIZZLE_128B) fills a 4-stage shared-memory
 //                           ring, ONE elected thread issues tcgen05.mma (cta_group::1, kind::f16, bf16 x bf16 ->
-//                           fp32) into a double-buffered TMEM accumulator (2 x 256 columns), four epilogue warps
+//                           fp32) into a double-buffered TMEM accumulator (2 x 256 columns), eight epilogue warps
 //                           read it back with tcgen05.ld, add the bias, apply ReLU and store bf16 (or fp32) rows.
 //                           Persistent: one CTA per SM walks the (m, n) tiles; the 8 n-tiles of one m-block are
 //                           adjacent in the walk so the activation block is read from HBM once.
@@ -29,7 +29,8 @@
 #define PKW_BK 64
 #define PKW_STAGES 4
 #define PKW_KPAD0 640  // 617 input channels padded to a multiple of PKW_BK
-#define PKW_THREADS 192
+#define PKW_EPI_WARPS 8   // two per TMEM lane quarter, each takes half of the tile's 256 columns
+#define PKW_THREADS (64 + 32 * PKW_EPI_WARPS)
 #define PKW_A_BYTES (PKW_BM * PKW_BK * 2)
 #define PKW_B_BYTES (PKW_BN * PKW_BK * 2)
 #define PKW_STAGE_BYTES (PKW_A_BYTES + PKW_B_BYTES)
@@ -158,7 +159,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     }
     for (int i = 0; i < 2; ++i) {
       pk_mbar_init(tfull + i, 1);
-      pk_mbar_init(tempty + i, 4);
+      pk_mbar_init(tempty + i, PKW_EPI_WARPS);
     }
     pk_fence_mbar_init();
   }
@@ -234,6 +235,10 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   } else if (warp >= 2) {
     // ===== epilogue: TMEM -> registers -> bias, ReLU -> global =====
     const int quarter = warp & 3;  // a warp may only touch TMEM lanes 32 * (warp % 4) .. + 31
+    // eight epilogue warps: warps 2..5 take the first half of the tile's column chunks, warps 6..9 the second (round 2:
+    // with four warps the epilogue of a K = 640 tile took as long as its MMAs and held layer 0 at 44 % tensor-active)
+    constexpr int CHW = (PKW_BN / 32) / (PKW_EPI_WARPS / 4);
+    const int ch0 = ((warp - 2) >> 2) * CHW;
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int sp = tile / n_mn, mn = tile - sp * n_mn;
@@ -246,7 +251,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       const int row = mb * PKW_BM + quarter * 32 + lane;
       const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * PKW_BN);
 #pragma unroll 1
-      for (int ch = 0; ch < PKW_BN / 32; ++ch) {
+      for (int ch = ch0; ch < ch0 + CHW; ++ch) {
         uint32_t v[32];
         pkw_tmem_ld32(t0 + (uint32_t)(ch * 32), v);
         pkw_tmem_ld_wait();
