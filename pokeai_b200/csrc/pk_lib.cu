@@ -62,6 +62,7 @@ struct PkGlobal {
   int zero_by_tma = 1;
   unsigned long long* trace = nullptr;  // debug phase trace buffer (pk_debug_set_trace)
   // side stream of the wide backward: the HBM-bound column sums run beside the tensor-bound GEMMs (PK_WIDE_SIDE)
+  int wide_tma_store = 1;  // wide GEMM: bf16 outputs through shared memory + TMA stores (PK_WIDE_TMA_STORE)
   int wide_side = 1;
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -115,6 +116,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.zero_copy = env_int("PK_ZERO_COPY", 1, 0, 2);
   g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
   g.wide_side = env_int("PK_WIDE_SIDE", 1, 0, 1);
+  g.wide_tma_store = env_int("PK_WIDE_TMA_STORE", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   g.decide_tc = env_int("PK_DECIDE_TC", 0, 0, 2);
   return PK_OK;

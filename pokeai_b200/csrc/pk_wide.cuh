@@ -34,7 +34,9 @@
 #define PKW_A_BYTES (PKW_BM * PKW_BK * 2)
 #define PKW_B_BYTES (PKW_BN * PKW_BK * 2)
 #define PKW_STAGE_BYTES (PKW_A_BYTES + PKW_B_BYTES)
-#define PKW_SMEM_BYTES (PKW_STAGES * PKW_STAGE_BYTES + 1024 + 256)
+#define PKW_OUT_STAGE_BYTES 2048  // one epilogue warp's 32 x 32 bf16 block on its way to a TMA store
+#define PKW_OUT_BYTES (PKW_EPI_WARPS * 2 * PKW_OUT_STAGE_BYTES)  // double-buffered per warp
+#define PKW_SMEM_BYTES (PKW_STAGES * PKW_STAGE_BYTES + PKW_OUT_BYTES + 1024 + 256)
 
 // ---- PTX wrappers --------------------------------------------------------------------------------------
 __device__ __forceinline__ void pkw_mbar_arrive(uint64_t* bar) {
@@ -46,6 +48,12 @@ __device__ __forceinline__ void pkw_tma_load_2d(void* sdst, const CUtensorMap* m
           pk_smem_u32(sdst)),
       "l"(map), "r"(pk_smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
+}
+// TMA 2-D store shared -> global (bulk async-group completion); out-of-bounds rows / columns of the box are clipped
+__device__ __forceinline__ void pkw_tma_store_2d(const CUtensorMap* map, const void* ssrc, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+               "r"(pk_smem_u32(ssrc)), "r"(c0), "r"(c1)
+               : "memory");
 }
 __device__ __forceinline__ void pkw_prefetch_map(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
@@ -123,6 +131,7 @@ struct PkwGemmArgs {
   const __nv_bfloat16* relu_mask;  // (M, N) bf16 or null: out = mask > 0 ? acc : 0 (backward through a ReLU)
   int M, N, K;            // N % 32 == 0; tails in M, N (to 256) and K (to 64) are zero-filled by TMA
   int relu;
+  int tma_store;          // out_bf (and only out_bf) is written by TMA stores through map_o
   int ksplit;             // >= 1: the contraction is cut into ksplit ranges; range s writes out_f32 + s * M * N
 };
 
@@ -132,12 +141,13 @@ struct PkwGemmArgs {
 template <int MN>
 __global__ void __launch_bounds__(PKW_THREADS, 1)
 pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
-                    PkwGemmArgs g) {
+                    const __grid_constant__ CUtensorMap map_o, PkwGemmArgs g) {
   extern __shared__ unsigned char pkw_smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte alignment
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(pkw_smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* tiles = smem;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + PKW_STAGES * PKW_STAGE_BYTES);
+  unsigned char* out_stage = smem + PKW_STAGES * PKW_STAGE_BYTES;  // 1024-byte aligned: SWIZZLE_64B staging
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + PKW_STAGES * PKW_STAGE_BYTES + PKW_OUT_BYTES);
   uint64_t* empty = full + PKW_STAGES;
   uint64_t* tfull = empty + PKW_STAGES;
   uint64_t* tempty = tfull + 2;
@@ -153,6 +163,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (threadIdx.x == 0) {
     pkw_prefetch_map(&map_a);
     pkw_prefetch_map(&map_w);
+    if (g.tma_store) pkw_prefetch_map(&map_o);
     for (int i = 0; i < PKW_STAGES; ++i) {
       pk_mbar_init(full + i, 1);
       pk_mbar_init(empty + i, 1);
@@ -239,6 +250,12 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     // with four warps the epilogue of a K = 640 tile took as long as its MMAs and held layer 0 at 44 % tensor-active)
     constexpr int CHW = (PKW_BN / 32) / (PKW_EPI_WARPS / 4);
     const int ch0 = ((warp - 2) >> 2) * CHW;
+    // bf16 outputs leave through shared memory and TMA: the block is written in the SWIZZLE_64B order the store expects
+    // (16-byte piece j of row r at piece j ^ ((r >> 1) & 3): conflict-free for a warp's 16-byte stores) and ONE thread
+    // hands 32 rows x 64 B to the copy engine.  With direct stores every warp-level store instruction touched 32
+    // different lines (one 16-byte piece of each of 32 rows 4 KB apart): 4 096 line accesses per 128 x 256 tile.
+    unsigned char* my_stage = out_stage + (warp - 2) * (2 * PKW_OUT_STAGE_BYTES);
+    int sbuf = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int sp = tile / n_mn, mn = tile - sp * n_mn;
@@ -288,7 +305,31 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             }
           }
         }
-        if (row < g.M) {
+        if (g.tma_store) {
+          if (lane == 0) pk_bulk_wait_read<1>();  // the store that read this staging buffer two chunks ago is done with it
+          __syncwarp();
+          unsigned char* st = my_stage + sbuf * PKW_OUT_STAGE_BYTES;
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 o;
+            __nv_bfloat162 p0 = __floats2bfloat162_rn(f[j], f[j + 1]);
+            __nv_bfloat162 p1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+            __nv_bfloat162 p2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]);
+            __nv_bfloat162 p3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+            o.x = *reinterpret_cast<uint32_t*>(&p0);
+            o.y = *reinterpret_cast<uint32_t*>(&p1);
+            o.z = *reinterpret_cast<uint32_t*>(&p2);
+            o.w = *reinterpret_cast<uint32_t*>(&p3);
+            *reinterpret_cast<uint4*>(st + lane * 64 + ((((j >> 3) ^ (lane >> 1)) & 3) << 4)) = o;
+          }
+          pk_fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            pkw_tma_store_2d(&map_o, st, n0, mb * PKW_BM + quarter * 32);
+            pk_bulk_commit();
+          }
+          sbuf ^= 1;
+        } else if (row < g.M) {
           if (g.out_bf != nullptr) {
             uint4* dst = reinterpret_cast<uint4*>(g.out_bf + (size_t)row * g.N + n0);
 #pragma unroll
@@ -317,6 +358,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       if (lane == 0) pkw_mbar_arrive(tempty + as);
     }
   }
+  if (warp >= 2 && lane == 0) pk_bulk_wait_all();  // TMA stores of the last tiles (no-op when none were issued)
   pkw_tc_fence_before();
   __syncthreads();
   if (warp == 1) {
