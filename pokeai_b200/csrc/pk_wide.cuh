@@ -142,9 +142,11 @@ template <int MN>
 __global__ void __launch_bounds__(PKW_THREADS, 1)
 pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_o, PkwGemmArgs g) {
-  extern __shared__ unsigned char pkw_smem_raw[];
-  // SWIZZLE_128B tiles need 1024-byte alignment
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(pkw_smem_raw) + 1023) & ~(uintptr_t)1023);
+  // SWIZZLE_128B tiles need 1024-byte alignment: asked for in the declaration, so that the accesses stay in the shared
+  // address space (STS / LDS instead of generic stores and loads)
+  extern __shared__ __align__(1024) unsigned char pkw_smem[];
+  unsigned char* smem = pkw_smem;
+  if ((pk_smem_u32(smem) & 1023u) != 0u) __trap();
   unsigned char* tiles = smem;
   unsigned char* out_stage = smem + PKW_STAGES * PKW_STAGE_BYTES;  // 1024-byte aligned: SWIZZLE_64B staging
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + PKW_STAGES * PKW_STAGE_BYTES + PKW_OUT_BYTES);
