@@ -229,6 +229,20 @@ PK_API size_t pk_dqn_scratch_floats(int n_layers, int n_channels, int in_channel
 PK_API int pk_dqn_grad(const float* prepared, const float* prepared_target, int n_layers, int n_channels, int A,
                 const pk_batch* batch, float gamma, int double_dqn, float* grad, float* loss,
                 float* scratch, void* stream);
+/* pk_dqn_grad for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has no counterpart in the reference.
+ * Same arguments, arithmetic and results as pk_dqn_grad minus `scratch`: the scratch is a file-scope device
+ * array inside the library of PK_DQN_STATIC_SCRATCH_FLOATS floats (32 MiB, held by every GPU that loads the library
+ * until the process exits), and the call performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ * Limit: pk_dqn_scratch_floats(n_layers, n_channels, in_channels, batch->n) must not exceed
+ * PK_DQN_STATIC_SCRATCH_FLOATS (the default 2 x 64 network on a 148-SM GPU: up to ~185 000 transitions); larger
+ * requests fail with PK_ERR_INVALID and a message, before anything is launched.  Every call on a device shares the
+ * one array: calls whose kernels may overlap on the GPU (different streams, no ordering between them) RACE -- keep
+ * them on one stream or order them with events.  The array keeps the previous call's contents; nothing in it needs
+ * to start at zero (each call writes what it reads). */
+#define PK_DQN_STATIC_SCRATCH_FLOATS (8u << 20)
+PK_API int pk_dqn_grad_static(const float* prepared, const float* prepared_target, int n_layers, int n_channels, int A,
+                       const pk_batch* batch, float gamma, int double_dqn, float* grad, float* loss, void* stream);
 /* clamp(grad, -1, 1) then Adam (torch defaults, no weight decay) on the flat parameter
  * vector; also writes the new values into `prepared` (may be NULL).  step is 1-based. */
 PK_API int pk_clamp_adam(float* params, const float* grad, float* exp_avg, float* exp_avg_sq, int n_layers,

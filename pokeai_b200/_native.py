@@ -81,6 +81,7 @@ _SIGNATURES = {
     "pk_wide_forward": (C.c_int, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, C.POINTER(pk_select_params), _vp]),
     "pk_dqn_scratch_floats": (_sz, [_i, _i, _i, _i]),
     "pk_dqn_grad": (C.c_int, [_vp, _vp, _i, _i, _i, C.POINTER(pk_batch), _f, _i, _vp, _vp, _vp, _vp]),
+    "pk_dqn_grad_static": (C.c_int, [_vp, _vp, _i, _i, _i, C.POINTER(pk_batch), _f, _i, _vp, _vp, _vp]),
     "pk_clamp_adam": (C.c_int, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _f, _f, _i, _vp, _vp]),
     "pk_update_ctl_advance": (C.c_int, [_vp, _vp]),
     "pk_clamp_adam_ctl": (C.c_int, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),

@@ -66,8 +66,18 @@ struct PkGlobal {
   int wide_side = 1;
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // pk_dqn_grad_static: device address of pk_static_scratch on `device` (cudaGetSymbolAddress in pk_init) and the
+  // return code of that query
+  float* static_scratch = nullptr;
+  int static_scratch_device = -1;
+  cudaError_t static_scratch_rc = cudaErrorNotReady;
 };
 static PkGlobal g;
+
+// Scratch of pk_dqn_grad_static, the entry point that allocates nothing: file-scope device memory, held by every GPU
+// that loads the library until the process exits.  In HOST code this name is only a stand-in for the symbol, not a
+// device address: kernels get the pointer cudaGetSymbolAddress returned for the current device (pk_init).
+static __device__ __align__(256) float pk_static_scratch[PK_DQN_STATIC_SCRATCH_FLOATS];
 
 static int env_int(const char* name, int dflt, int lo, int hi) {
   const char* v = getenv(name);
@@ -102,6 +112,16 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   for (int i = 0; i < t->n_species; ++i) g.tab.type_mask[i] = t->species_type_mask[i] & ((1u << PK_N_TYPES) - 1u);
   PK_CUDA(cudaMemcpyToSymbol(c_tab, &g.tab, sizeof(g.tab)));
   g.device = device;
+  {  // once per device, with that device current; a failure only disables pk_dqn_grad_static, which reports it
+    void* p = nullptr;
+    g.static_scratch_rc = cudaGetSymbolAddress(&p, pk_static_scratch);
+    if (g.static_scratch_rc != cudaSuccess) {
+      (void)cudaGetLastError();
+      p = nullptr;
+    }
+    g.static_scratch = reinterpret_cast<float*>(p);
+    g.static_scratch_device = device;
+  }
   g.sm_count = prop.multiProcessorCount;
   g.max_smem = (int)prop.sharedMemPerBlockOptin;
   g.decide_warps = env_int("PK_DECIDE_WARPS", 16, 1, 32);
@@ -478,6 +498,31 @@ extern "C" int pk_select(const float* q, const int32_t* mask, int B, int A, cons
 
 // ---- DQN update ---------------------------------------------------------------------------------------
 #include "pk_update_api.inc"
+
+// pk_dqn_grad without caller scratch and without any allocation: the scratch is pk_static_scratch (above).  No
+// counterpart in the reference; added for callers that cannot allocate.
+// Nothing in the scratch has to start at zero: every word pk_dqn_grad reads it has written in the same call (a*,
+// next-state values, one gradient partial per launched CTA; the atomics fallback clears its sum with a memset node on
+// the stream), so the previous call's contents are simply overwritten.
+extern "C" int pk_dqn_grad_static(const float* prepared, const float* prepared_target, int n_layers, int n_channels, int A,
+                                  const pk_batch* batch, float gamma, int double_dqn, float* grad, float* loss,
+                                  void* stream) {
+  PK_CHECK_INIT();
+  PK_REQUIRE(batch != nullptr, "pk_dqn_grad_static: null batch");
+  PK_REQUIRE(batch->n >= 1, "pk_dqn_grad_static: need n >= 1 (got %d)", batch->n);
+  PK_REQUIRE(n_layers >= 1 && n_layers <= PK_UPD_MAX_LAYERS && n_channels >= 1, "pk_dqn_grad_static: bad network shape");
+  if (g.static_scratch == nullptr || g.static_scratch_device != g.device)
+    return pk_fail(PK_ERR_CUDA, "pk_dqn_grad_static: the static scratch has no device address on device %d (%s)", g.device,
+                   cudaGetErrorString(g.static_scratch_rc));
+  const size_t need = pk_scratch_layout(pk_make_layout(n_layers, n_channels, g.tab.C), batch->n).total;
+  if (need > (size_t)PK_DQN_STATIC_SCRATCH_FLOATS)
+    return pk_fail(PK_ERR_INVALID,
+                   "pk_dqn_grad_static: %d transitions on a %d x %d network need %zu scratch floats, the static scratch "
+                   "holds %zu; use pk_dqn_grad with caller-owned scratch",
+                   batch->n, n_layers, n_channels, need, (size_t)PK_DQN_STATIC_SCRATCH_FLOATS);
+  return pk_dqn_grad(prepared, prepared_target, n_layers, n_channels, A, batch, gamma, double_dqn, grad, loss,
+                     g.static_scratch, stream);
+}
 
 // ---- host-buffer session ------------------------------------------------------------------------------
 struct pk_session {
