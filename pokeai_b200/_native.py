@@ -58,6 +58,7 @@ _SIGNATURES = {
     "pk_set_overlap_launches": (C.c_int, [_i]),
     "pk_debug_set_pairing": (C.c_int, [_i]),
     "pk_debug_set_decide_tc": (C.c_int, [_i]),
+    "pk_debug_set_dense_tc": (C.c_int, [_i]),
     "pk_debug_set_hidden_tc": (C.c_int, [_i]),
     "pk_n_channels": (C.c_int, []),
     "pk_sm_count": (C.c_int, []),

@@ -56,8 +56,12 @@ struct PkDeviceTables {
 //                  read by the backward pass (dh = W^T dz)           <- `total_train` ends here
 //   tc[l] (HP == 64 only, l = 1..n_layers-1): the same hidden matrix as the B operand of tcgen05.mma.kind::tf32 --
 //                  two 64 x 64 fp32 tiles, hi = tf32(w) and lo = w - hi, each in the K-major SWIZZLE_128B shared-memory
-//                  layout (pk_tc_tile_off), so pk_decide_tc_kernel stages them with one TMA bulk load   <- `total_all`
+//                  layout (pk_tc_tile_off), so pk_decide_tc_kernel stages them with one TMA bulk load
+//   tc0 (HP == 64 only): W0 for pk_dense_tc_kernel -- per k-block of 32 input rows one 128-row K-major SWIZZLE_128B tile,
+//                  rows 0-63 = tf32(W0[j][k]), rows 64-127 = the remainders (hi element + PK_TC0_LO_DELTA), zero padded
+//                  beyond C and H; ceil(C / 32) tiles of PK_TC_TILE_FLOATS                            <- `total_all`
 #define PK_TC_TILE_FLOATS 4096u
+#define PK_TC0_LO_DELTA 2048u  // 64 rows of 32 floats
 struct PkLayout {
   int C, H, HP, n_layers;
   unsigned w1t, wout, bout, total, total_train, total_all;
@@ -65,6 +69,7 @@ struct PkLayout {
   unsigned wl[PK_MAX_LAYERS];
   unsigned wn[PK_MAX_LAYERS];
   unsigned tc[PK_MAX_LAYERS];
+  unsigned tc0;  // layer 0 as tensor-core B operand, see below (0 when HP != 64)
 };
 
 // float offset of element (row, k) of a K-major SWIZZLE_128B fp32 operand tile with 64 rows x 64 k: k-blocks of 32
@@ -125,6 +130,11 @@ __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
       L.tc[l] = 0;
     }
   }
+  L.tc0 = 0;
+  if (L.HP == 64) {
+    L.tc0 = o;
+    o += (unsigned)((C + 31) >> 5) * PK_TC_TILE_FLOATS;
+  }
   L.total_all = o;
   return L;
 }
@@ -166,8 +176,8 @@ __host__ __device__ inline PkParamLayout pk_make_param_layout(int n_layers, int 
   return P;
 }
 
-// *tc_off (optional) = offset of the hi element in the tensor-core tile of a hidden-layer weight (lo at
-// + PK_TC_TILE_FLOATS), 0 when the layout has none
+// *tc_off (optional) = offset of the hi element in the tensor-core tile of a weight (lo at + pk_tc_lo_delta), 0 when
+// the layout has none
 __host__ __device__ inline unsigned pk_flat_to_prepared(const PkParamLayout& P, const PkLayout& L, unsigned i,
                                                         unsigned* wn_off, unsigned* tc_off) {
   *wn_off = 0;
@@ -178,12 +188,18 @@ __host__ __device__ inline unsigned pk_flat_to_prepared(const PkParamLayout& P, 
       const unsigned j = e / cin, k = e - j * cin;
       if (l > 0) *wn_off = L.wn[l] + j * L.HP + k;
       if (l > 0 && tc_off && L.tc[l]) *tc_off = L.tc[l] + pk_tc_tile_off(j, k, 2048u);
+      if (l == 0 && tc_off && L.tc0) *tc_off = L.tc0 + pk_tc_tile_off(j, k, PK_TC_TILE_FLOATS);
       return (l == 0 ? L.w1t : L.wl[l]) + k * L.HP + j;
     }
     if (i < P.b[l] + (unsigned)P.H) return L.b[l] + (i - P.b[l]);
   }
   if (i < P.bout) return L.wout + (i - P.wout);
   return L.bout;
+}
+
+// distance from the hi element of a tensor-core tile to its lo element
+__host__ __device__ inline unsigned pk_tc_lo_delta(const PkLayout& L, unsigned tc_off) {
+  return (L.tc0 && tc_off >= L.tc0) ? PK_TC0_LO_DELTA : PK_TC_TILE_FLOATS;
 }
 
 struct PkSelect {

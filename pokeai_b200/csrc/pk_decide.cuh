@@ -1095,3 +1095,15 @@ __global__ void pk_tc_tiles_kernel(const float* __restrict__ src, float* __restr
   dst[off] = hi;
   dst[off + PK_TC_TILE_FLOATS] = w - hi;
 }
+// W0 (rows, cols) row-major -> PkLayout::tc0: per k-block of 32 input rows a 128-row tile, rows 0-63 tf32(w), rows
+// 64-127 the remainders, zero padded (pk_dense_tc_kernel's B operand)
+__global__ void pk_tc0_tiles_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int cols, int nkb) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * 32 * nkb) return;
+  const int k = i % (32 * nkb), j = i / (32 * nkb);
+  const float w = (j < rows && k < cols) ? src[(size_t)j * cols + k] : 0.0f;
+  const float hi = pk_tf32_hi(w);
+  const unsigned off = pk_tc_tile_off((unsigned)j, (unsigned)k, PK_TC_TILE_FLOATS);
+  dst[off] = hi;
+  dst[off + PK_TC0_LO_DELTA] = w - hi;
+}

@@ -1,0 +1,464 @@
+// Dense-input forward on the tensor cores: feat (B, C, A) fp32 -> q (B, A), 64-channel networks.
+//
+// pk_dense_forward_kernel (pk_decide.cuh) walks the dense block row by row on the FP32 pipe: ~5 800 warp instructions
+// per battle, 0.39 of the HBM roofline.  The block is dense in memory but the contraction does not care: layer 0 is
+// the GEMM  H0[(b, a)][j] = sum_k X[b][k][a] W0[j][k],  and this kernel runs it -- and the hidden layers -- with
+// tcgen05.mma.kind::tf32 on operands split x = hi + lo (hi = tf32(x), lo = x - hi exact), accumulating
+// hi*hi + hi*lo + lo*hi in fp32 in TMEM, which keeps Q inside the 1e-5 fp32 tolerance of the parity tests.
+//
+//   tile       nb = 128 / A consecutive battles = nb * A accumulator rows (126 at A = 9); row r = (battle r / A,
+//              action column r % A), which is also the flat index of q -- the result store is one coalesced run.
+//   X stream   a battle's k-block (32 feature rows x A columns) is 128 A contiguous bytes at a 4-byte-aligned address.
+//              Warp w copies the 16-byte-aligned cover of the pieces of battles w, w + 16 with 16-byte cp.async into a
+//              ring of X stages, XS - 1 k-blocks ahead of use; completion is counted on an mbarrier
+//              (cp.async.mbarrier.arrive.noinc).  Nothing is read twice.
+//   A operand  lives in TENSOR MEMORY, not shared memory (tcgen05.mma with A from TMEM): accumulator row r is TMEM
+//              lane r, and thread (lane quarter q = warp % 4, lane t) owns row 32 q + t.  The four warps of a quarter
+//              split the k-block's 32 feature rows: warp group cg = warp / 4 reads X[row][8 cg .. 8 cg + 7] -- eight
+//              LDS whose lanes walk consecutive words -- splits them and writes 8 hi + 8 lo columns with one
+//              tcgen05.st.  No transposed copy in shared memory and no proxy fence: the shared-memory pipe, which bound
+//              the first version of this kernel (A tiles in shared memory: 136 KB of traffic per 16 KB k-block), carries
+//              the X stream once in and once out, and W0.  When every lo of a k-block is zero (one-hot rows are exact
+//              in tf32) the lo MMA is skipped.
+//   W0         per k-block a 128-row B operand [tf32(W0) ; W0 - tf32(W0)] (16 KB, PkLayout::tc0, kept current by
+//              pk_clamp_adam), streamed from L2 with one TMA bulk load per k-block: MMA N = 128 gives X_hi W_hi in
+//              accumulator columns 0-63 and X_hi W_lo in 64-127; the N = 64 lo MMA adds X_lo W_hi to columns 0-63.
+//   MMA warp   one thread issues; tcgen05.commit releases the stages.
+//   epilogue   the sixteen warps again: thread (row, cg) reads channels 16 cg .. +15 of its row from the accumulator,
+//              adds the two halves and the bias, applies ReLU, splits and writes the hidden layer's A operand -- also in
+//              TMEM; the hidden MMAs read the hidden matrices (PkLayout::tc) from shared memory; the head is a 16-channel
+//              partial dot product per thread, summed in a fixed order through shared memory.
+//
+// Tensor memory (512 columns): layer-0 accumulator 128, hidden accumulator 64, hidden A operand 128, A stages 3 x 64.
+// Reference semantics: MLPModel.forward mlp_model.py:21-30 on Agent._calc_q_vector[_batch] input (agent.py:23-30).
+#pragma once
+
+#include "pk_decide_tc.cuh"
+
+#define PKD_TW 16                   // loading / splitting / epilogue warps
+#define PKD_PRODUCER PKD_TW         // warp index of the TMA producer (W0 stream)
+#define PKD_MMA (PKD_TW + 1)        // warp index of the MMA issuer
+#define PKD_WARPS (PKD_TW + 2)
+#define PKD_A_STAGES 3
+#define PKD_W_STAGE 16384u          // [W0 hi ; W0 lo] of one k-block: 128 rows x 128 B
+#define PKD_W_STAGES 3
+#define PKD_X_STAGES_MAX 8
+#define PKD_TMEM_COLS 512u
+#define PKD_COL_ACC0 0u             // layer-0 accumulator: X_hi W_hi + X_lo W_hi | X_hi W_lo
+#define PKD_COL_HACC 128u           // hidden-layer accumulator
+#define PKD_COL_HA 192u             // hidden A operand: per K-step of 8: hi (8 columns), lo (8 columns)
+#define PKD_COL_A 320u              // A stages, 64 columns each, same K-step layout
+
+struct PkdSmemPlan {
+  unsigned w;         // W0 k-block stages
+  unsigned w1;        // hidden matrices as B operands (PkLayout::tc), PKT_SET_BYTES each
+  unsigned x;         // X stages
+  unsigned x_stage, x_stages, piece;  // bytes per stage, stages, bytes per battle slot
+  unsigned small;     // b[0..n_layers-1], wout, bout
+  unsigned part;      // head partials [4][128]
+  unsigned flags;     // "some lo is non-zero" per (A stage, phase)
+  unsigned bars;
+  unsigned total;
+};
+
+// battles per 128-row tile (warp w copies battles w, w + 16: two passes at most)
+__host__ __device__ inline int pkd_battles_per_tile(int A) { return 128 / A < 32 ? 128 / A : 32; }
+
+__host__ __device__ inline PkdSmemPlan pkd_smem_plan(const PkLayout& lay, int A, unsigned max_smem) {
+  PkdSmemPlan p;
+  const unsigned nb = (unsigned)pkd_battles_per_tile(A);
+  unsigned o = 0;
+  p.w = o;
+  o += PKD_W_STAGE * PKD_W_STAGES;
+  p.w1 = o;
+  o += PKT_SET_BYTES * (unsigned)(lay.n_layers - 1);
+  p.small = o;
+  o += ((unsigned)lay.n_layers * PKT_H + PKT_H + 4u) * 4u;
+  p.part = o;
+  o += 4u * 128u * 4u;
+  p.flags = o;
+  o += 32u;
+  p.bars = o;
+  o += 8u * (2u * PKD_X_STAGES_MAX + 2u * PKD_A_STAGES + 2u * PKD_W_STAGES + 4u) + 16u;
+  o = (o + 127u) & ~127u;
+  p.x = o;
+  p.piece = 128u * (unsigned)A + 32u;  // the aligned cover of 128 A bytes at any 4-byte alignment
+  p.x_stage = (nb * p.piece + 127u) & ~127u;
+  const unsigned room = max_smem > o + 1024u ? max_smem - o - 1024u : 0u;
+  p.x_stages = room / p.x_stage;
+  if (p.x_stages > PKD_X_STAGES_MAX) p.x_stages = PKD_X_STAGES_MAX;
+  p.total = o + p.x_stages * p.x_stage + 1024u;
+  return p;
+}
+
+// 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void pkd_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void pkd_tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ void pkd_tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float pkd_lds(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+// D[tmem] (+)= A[tmem] * B[smem desc], kind::tf32
+__device__ __forceinline__ void pkd_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+
+// sixteen values of one row -> two K-steps of an A operand in TMEM: per K-step hi (8 columns) then lo (8 columns)
+__device__ __forceinline__ void pkd_split_store16(uint32_t taddr, const float (&x)[16]) {
+#pragma unroll
+  for (int s = 0; s < 2; ++s) {
+    uint32_t v[16];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float hi = pk_tf32_hi(x[8 * s + j]);
+      v[j] = __float_as_uint(hi);
+      v[8 + j] = __float_as_uint(x[8 * s + j] - hi);
+    }
+    pkd_tmem_st16(taddr + 16u * (uint32_t)s, v);
+  }
+}
+
+// debug timeline (pk_debug_set_trace): SM clock of CTA 0 at point p of iteration it < 128 of role 0 (warp 0),
+// 1 (MMA thread), 2 (producer lane 0); trace == nullptr in normal operation
+__device__ __forceinline__ void pkd_trace(unsigned long long* tr, int role, uint32_t it, int p) {
+  if (tr != nullptr && it < 128u) tr[((size_t)role * 128 + it) * 8 + p] = (unsigned long long)clock64();
+}
+
+__global__ void __launch_bounds__(PKD_WARPS * 32, 1)
+pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __restrict__ prep, PkLayout lay,
+                   float* __restrict__ q, unsigned max_smem, unsigned long long* __restrict__ trace) {
+  constexpr int HP = PKT_H;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  if ((pk_smem_u32(smem) & 1023u) != 0u) __trap();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const PkdSmemPlan plan = pkd_smem_plan(lay, A, max_smem);
+  const int XS = (int)plan.x_stages;
+  const int nb = pkd_battles_per_tile(A), rows = nb * A;
+  const int L = lay.C * A;
+  const int NKB = (lay.C + 31) >> 5;
+  const int ntiles = (B + nb - 1) / nb;
+  const int n_hidden = lay.n_layers - 1;  // >= 1
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + plan.bars);
+  uint64_t* x_full = bars;
+  uint64_t* x_empty = x_full + PKD_X_STAGES_MAX;
+  uint64_t* a_full = x_empty + PKD_X_STAGES_MAX;
+  uint64_t* a_empty = a_full + PKD_A_STAGES;
+  uint64_t* w_full = a_empty + PKD_A_STAGES;
+  uint64_t* w_empty = w_full + PKD_W_STAGES;
+  uint64_t* acc0_full = w_empty + PKD_W_STAGES;
+  uint64_t* hid_full = acc0_full + 1;
+  uint64_t* hidacc_full = hid_full + 1;
+  uint64_t* wbar = hidacc_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wbar + 1);
+  volatile uint32_t* lo_flag = reinterpret_cast<volatile uint32_t*>(smem + plan.flags);  // [A stage][phase]
+  float* s_small = reinterpret_cast<float*>(smem + plan.small);
+  float* s_part = reinterpret_cast<float*>(smem + plan.part);
+  const uint32_t w_u32 = pk_smem_u32(smem + plan.w), w1_u32 = pk_smem_u32(smem + plan.w1);
+  const uint32_t x_u32 = pk_smem_u32(smem + plan.x);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < PKD_X_STAGES_MAX; ++i) {
+      pk_mbar_init(x_full + i, PKD_TW * 32);  // every copying thread (cp.async.mbarrier.arrive.noinc)
+      pk_mbar_init(x_empty + i, PKD_TW);
+    }
+    for (int i = 0; i < PKD_A_STAGES; ++i) {
+      pk_mbar_init(a_full + i, PKD_TW);
+      pk_mbar_init(a_empty + i, 1);
+    }
+    for (int i = 0; i < PKD_W_STAGES; ++i) {
+      pk_mbar_init(w_full + i, 1);
+      pk_mbar_init(w_empty + i, 1);
+    }
+    pk_mbar_init(acc0_full, 1);
+    pk_mbar_init(hid_full, PKD_TW);
+    pk_mbar_init(hidacc_full, 1);
+    pk_mbar_init(wbar, 1);
+    for (int i = 0; i < 2 * PKD_A_STAGES; ++i) lo_flag[i] = 0u;
+    pk_fence_mbar_init();
+  }
+  if (warp == 0) pkw_tmem_alloc(tmem_slot, PKD_TMEM_COLS);
+  pkw_tc_fence_before();
+  __syncthreads();
+  pkw_tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == PKD_PRODUCER) {
+    // ---- TMA producer: biases / head / hidden operands once, then the W0 k-blocks in consumption order ----
+    if (lane == 0) {
+      pk_mbar_expect_tx(wbar, (uint32_t)(lay.n_layers * HP + HP + 4) * 4u + (uint32_t)n_hidden * PKT_SET_BYTES);
+      for (int l = 0; l < lay.n_layers; ++l) pk_bulk_load(s_small + HP * l, prep + lay.b[l], HP * 4u, wbar);
+      pk_bulk_load(s_small + HP * lay.n_layers, prep + lay.wout, HP * 4u, wbar);
+      pk_bulk_load(s_small + HP * lay.n_layers + HP, prep + lay.bout, 16u, wbar);
+      for (int l = 1; l <= n_hidden; ++l)
+        pk_bulk_load(smem + plan.w1 + (unsigned)(l - 1) * PKT_SET_BYTES, prep + lay.tc[l], PKT_SET_BYTES, wbar);
+      uint32_t wit = 0;
+      unsigned long long* ptr = blockIdx.x == 0 ? trace : nullptr;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int kb = 0; kb < NKB; ++kb, ++wit) {
+          const int ws = (int)(wit % PKD_W_STAGES);
+          const uint32_t wph = (wit / PKD_W_STAGES) & 1u;
+          pkd_trace(ptr, 2, wit, 0);
+          pk_mbar_wait(w_empty + ws, wph ^ 1u);
+          pkd_trace(ptr, 2, wit, 1);
+          pk_mbar_expect_tx(w_full + ws, PKD_W_STAGE);
+          pk_bulk_load(smem + plan.w + (unsigned)ws * PKD_W_STAGE, prep + lay.tc0 + (size_t)kb * (PKD_W_STAGE >> 2),
+                       PKD_W_STAGE, w_full + ws);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == PKD_MMA) {
+    // ---- MMA issuer ----
+    if (lane == 0) {
+      constexpr uint32_t idesc_hi = pkt_instr_desc(128, 128), idesc_lo = pkt_instr_desc(128, 64);
+      uint32_t ait = 0, wit = 0, hfpar = 0;
+      unsigned long long* mtr = blockIdx.x == 0 ? trace : nullptr;
+      pk_mbar_wait(wbar, 0);
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int kb = 0; kb < NKB; ++kb, ++ait, ++wit) {
+          const int as = (int)(ait % PKD_A_STAGES);
+          const uint32_t aph = (ait / PKD_A_STAGES) & 1u;
+          const int ws = (int)(wit % PKD_W_STAGES);
+          const uint32_t wph = (wit / PKD_W_STAGES) & 1u;
+          pkd_trace(mtr, 1, ait, 0);
+          pk_mbar_wait(a_full + as, aph);
+          pkd_trace(mtr, 1, ait, 1);
+          pk_mbar_wait(w_full + ws, wph);
+          pkd_trace(mtr, 1, ait, 2);
+          pkw_tc_fence_after();
+          const uint32_t fl = lo_flag[as * 2 + (int)aph];
+          lo_flag[as * 2 + (int)aph] = 0u;  // set again two uses of this stage later, after the commit below
+          const uint32_t ta = tmem_base + PKD_COL_A + 64u * (uint32_t)as, tw = w_u32 + (uint32_t)ws * PKD_W_STAGE;
+#pragma unroll
+          for (int s = 0; s < 4; ++s) {  // UMMA_K = 8 fp32: 16 TMEM columns (hi | lo) of A, 32 B of the swizzle atom of W
+            const uint64_t bd = pkw_smem_desc_k128(tw) + 2u * (uint64_t)s;
+            pkd_mma_ts(tmem_base + PKD_COL_ACC0, ta + 16u * (uint32_t)s, bd, idesc_hi, (kb | s) != 0 ? 1u : 0u);
+            if (fl) pkd_mma_ts(tmem_base + PKD_COL_ACC0, ta + 16u * (uint32_t)s + 8u, bd, idesc_lo, 1u);
+          }
+          pkd_trace(mtr, 1, ait, 3);
+          pkw_mma_commit(w_empty + ws);
+          pkw_mma_commit(a_empty + as);
+          pkd_trace(mtr, 1, ait, 4);
+        }
+        pkw_mma_commit(acc0_full);
+        for (int l = 1; l <= n_hidden; ++l) {
+          pk_mbar_wait(hid_full, hfpar);
+          hfpar ^= 1u;
+          pkw_tc_fence_after();
+          // D (128 x 64) = H (128 x 64, TMEM) . W_l^T:  lo*hi + hi*lo + hi*hi
+          constexpr uint32_t idesc_h = pkt_instr_desc(128, 64);
+          const uint32_t tb = w1_u32 + (uint32_t)(l - 1) * PKT_SET_BYTES;
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {
+            const uint32_t th = tmem_base + PKD_COL_HA + 16u * (uint32_t)s;
+            const uint64_t bhi = pkw_smem_desc_k128(tb + (uint32_t)(s >> 2) * PKT_KB_BYTES) + 2u * (uint64_t)(s & 3);
+            const uint64_t blo =
+                pkw_smem_desc_k128(tb + PKT_TILE_BYTES + (uint32_t)(s >> 2) * PKT_KB_BYTES) + 2u * (uint64_t)(s & 3);
+            pkd_mma_ts(tmem_base + PKD_COL_HACC, th + 8u, bhi, idesc_h, s != 0 ? 1u : 0u);
+            pkd_mma_ts(tmem_base + PKD_COL_HACC, th, blo, idesc_h, 1u);
+            pkd_mma_ts(tmem_base + PKD_COL_HACC, th, bhi, idesc_h, 1u);
+          }
+          pkw_mma_commit(hidacc_full);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- loading / splitting / epilogue warps ----
+    const int wq = warp & 3, cg = warp >> 2;  // TMEM lane quarter this warp may access; its k / channel group
+    const int row = 32 * wq + lane;           // this thread's accumulator row = TMEM lane
+    const bool row_ok = row < rows;
+    const int rbi = row / A;                  // its battle within the tile, its action column
+    const int ra = row - rbi * A;
+    const unsigned long long feat_addr = (unsigned long long)feat;
+    const uint32_t tlane = tmem_base + ((uint32_t)(32 * wq) << 16);
+    // element (k, ra) of this row's battle inside a stage: piece rbi, float index k * A + ra (+ the piece's misalignment)
+    const uint32_t src_row = (uint32_t)rbi * plan.piece + (uint32_t)ra * 4u + (uint32_t)(8 * cg * A) * 4u;
+    uint32_t xit = 0, ait = 0, tpar = 0, hpar = 0;
+    bool first = true;
+    unsigned long long* ttr = (blockIdx.x == 0 && threadIdx.x == 0) ? trace : nullptr;
+    // X copies: warp w brings in the pieces of battles w, w + 16 of a tile -- the 16-byte-aligned cover of each piece,
+    // 16 bytes per lane and cp.async -- XS - 1 k-blocks ahead of their use, across tile boundaries
+    const unsigned long long arr_end = feat_addr + (unsigned long long)B * L * 4ull;
+    uint32_t iit = 0;  // iteration the next issue is for
+    int itile = blockIdx.x, ikb = 0;
+    auto issue = [&]() {
+      if (itile < ntiles) {
+        const uint32_t sbase = x_u32 + (iit % (uint32_t)XS) * plan.x_stage;
+        const uint32_t len = (uint32_t)min(32, lay.C - ikb * 32) * (uint32_t)A * 4u;
+        for (int pb = warp; pb < nb; pb += PKD_TW) {
+          const long long b = (long long)itile * nb + pb;
+          if (b >= B) break;
+          const unsigned long long addr = feat_addr + 4ull * ((unsigned long long)b * L + (unsigned long long)ikb * 32 * A);
+          const uint32_t mis = (uint32_t)(addr & 15ull);
+          const unsigned long long src = addr - mis;
+          const uint32_t nch = (mis + len + 15u) >> 4;
+          const uint32_t dst = sbase + (uint32_t)pb * plan.piece;
+          for (uint32_t c = lane; c < nch; c += 32u) {
+            const unsigned long long g = src + 16ull * c;
+            if (g + 16ull <= arr_end) {
+              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * c), "l"(g) : "memory");
+            } else {  // the last chunk of the array: only the floats that exist
+              for (uint32_t e = 0; e < 16u && g + e + 4ull <= arr_end; e += 4u)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 16u * c + e), "l"(g + e) : "memory");
+            }
+          }
+        }
+      }
+      // counts as this thread's arrival once its copies above have landed (immediately if it made none)
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(pk_smem_u32(x_full + iit % (uint32_t)XS))
+                   : "memory");
+      ++iit;
+      if (++ikb == NKB) {
+        ikb = 0;
+        itile += gridDim.x;
+      }
+    };
+    for (int i = 0; i < XS - 1; ++i) issue();
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long b0 = (long long)tile * nb;
+      const uint32_t src_t =
+          src_row + (uint32_t)((feat_addr + 4ull * (unsigned long long)(b0 + rbi) * (unsigned long long)L) & 15ull);
+      for (int kb = 0; kb < NKB; ++kb, ++xit, ++ait) {
+        const int xs = (int)(xit % (uint32_t)XS);
+        const uint32_t xph = (xit / (uint32_t)XS) & 1u;
+        const int as = (int)(ait % PKD_A_STAGES);
+        const uint32_t aph = (ait / PKD_A_STAGES) & 1u;
+        pkd_trace(ttr, 0, xit, 0);
+        if (xit > 0) {  // refill the stage the previous iteration consumed (every warp has left it, or is about to)
+          const uint32_t j = xit - 1u;
+          pk_mbar_wait(x_empty + (int)(j % (uint32_t)XS), (j / (uint32_t)XS) & 1u);
+        }
+        pkd_trace(ttr, 0, xit, 1);
+        issue();
+        pkd_trace(ttr, 0, xit, 2);
+        pk_mbar_wait(x_full + xs, xph);
+        pkd_trace(ttr, 0, xit, 3);
+        const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_t;
+        const int k0 = kb * 32 + 8 * cg;
+        float x[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          x[j] = (row_ok && k0 + j < lay.C) ? pkd_lds(xb + (uint32_t)(j * A) * 4u) : 0.0f;
+        __syncwarp();
+        if (lane == 0) pkw_mbar_arrive(x_empty + xs);
+        pk_mbar_wait(a_empty + as, aph ^ 1u);
+        pkw_tc_fence_after();
+        pkd_trace(ttr, 0, xit, 4);
+        uint32_t v[16];
+        uint32_t lo_or = 0u;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float hi = pk_tf32_hi(x[j]), lo = x[j] - hi;
+          v[j] = __float_as_uint(hi);
+          v[8 + j] = __float_as_uint(lo);
+          lo_or |= __float_as_uint(lo);
+        }
+        pkd_tmem_st16(tlane + PKD_COL_A + 64u * (uint32_t)as + 16u * (uint32_t)cg, v);
+        const bool any_lo = __any_sync(0xffffffffu, (lo_or << 1) != 0u);
+        pkd_tmem_st_wait();
+        pkw_tc_fence_before();
+        __syncwarp();
+        pkd_trace(ttr, 0, xit, 5);
+        if (lane == 0) {
+          if (any_lo) lo_flag[as * 2 + (int)aph] = 1u;
+          pkw_mbar_arrive(a_full + as);
+        }
+      }
+      // ---- layer-0 epilogue: relu(D[:, j] + D[:, 64 + j] + b0[j]) -> the hidden layer's A operand (TMEM) ----
+      pkd_trace(ttr, 0, xit - 1u, 6);
+      pk_mbar_wait(acc0_full, tpar);
+      tpar ^= 1u;
+      pkw_tc_fence_after();
+      if (first) {
+        pk_mbar_wait(wbar, 0);
+        first = false;
+      }
+      {
+        uint32_t v1[16], v2[16];
+        pkd_tmem_ld16(tlane + PKD_COL_ACC0 + 16u * (uint32_t)cg, v1);
+        pkd_tmem_ld16(tlane + PKD_COL_ACC0 + 64u + 16u * (uint32_t)cg, v2);
+        pkw_tmem_ld_wait();
+        float h[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          h[j] = fmaxf((__uint_as_float(v1[j]) + __uint_as_float(v2[j])) + s_small[16 * cg + j], 0.0f);
+        pkd_split_store16(tlane + PKD_COL_HA + 32u * (uint32_t)cg, h);
+      }
+      pkd_tmem_st_wait();
+      pkw_tc_fence_before();
+      __syncwarp();
+      if (lane == 0) pkw_mbar_arrive(hid_full);
+      for (int l = 1; l <= n_hidden; ++l) {
+        pk_mbar_wait(hidacc_full, hpar);
+        hpar ^= 1u;
+        pkw_tc_fence_after();
+        uint32_t v[16];
+        pkd_tmem_ld16(tlane + PKD_COL_HACC + 16u * (uint32_t)cg, v);
+        pkw_tmem_ld_wait();
+        const float* bl = s_small + HP * l + 16 * cg;
+        if (l < n_hidden) {
+          float h[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) h[j] = fmaxf(__uint_as_float(v[j]) + bl[j], 0.0f);
+          pkd_split_store16(tlane + PKD_COL_HA + 32u * (uint32_t)cg, h);
+          pkd_tmem_st_wait();
+          pkw_tc_fence_before();
+          __syncwarp();
+          if (lane == 0) pkw_mbar_arrive(hid_full);
+        } else {
+          // head: this thread's 16 channels of q = w_out . relu(D + b) + b_out
+          const float* wo = s_small + HP * lay.n_layers + 16 * cg;
+          float p0 = 0.0f, p1 = 0.0f, p2 = 0.0f, p3 = 0.0f;
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const float4 bv = *reinterpret_cast<const float4*>(bl + j), wv = *reinterpret_cast<const float4*>(wo + j);
+            p0 = fmaf(wv.x, fmaxf(__uint_as_float(v[j]) + bv.x, 0.0f), p0);
+            p1 = fmaf(wv.y, fmaxf(__uint_as_float(v[j + 1]) + bv.y, 0.0f), p1);
+            p2 = fmaf(wv.z, fmaxf(__uint_as_float(v[j + 2]) + bv.z, 0.0f), p2);
+            p3 = fmaf(wv.w, fmaxf(__uint_as_float(v[j + 3]) + bv.w, 0.0f), p3);
+          }
+          s_part[128 * cg + row] = (p0 + p1) + (p2 + p3);
+          pkw_tc_fence_before();
+        }
+      }
+      pkt_named_barrier(1, 32 * PKD_TW);
+      pkd_trace(ttr, 0, xit - 1u, 7);
+      if (cg == 0) {
+        const long long o = b0 * A + row;
+        if (row_ok && o < (long long)B * A)
+          q[o] = ((s_part[row] + s_part[128 + row]) + (s_part[256 + row] + s_part[384 + row])) +
+                 s_small[HP * lay.n_layers + HP];
+      }
+      pkt_named_barrier(2, 32 * PKD_TW);  // s_part is rewritten by the next tile's head
+    }
+  }
+  pkw_tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    pkw_tc_fence_after();
+    pkw_tmem_dealloc(tmem_base, PKD_TMEM_COLS);
+  }
+}

@@ -13,6 +13,7 @@
 #include "pk_update.cuh"
 #include "pk_wide.cuh"
 #include "pk_decide_tc.cuh"
+#include "pk_dense_tc.cuh"
 
 // ---- error handling -----------------------------------------------------------------------------
 static thread_local char g_err[512] = "";
@@ -54,6 +55,7 @@ struct PkGlobal {
   // sessions, whose records always arrive from host memory (PK_PDL_SESSION=0 turns that off)
   int pdl = 0;
   int pdl_session = 1;
+  int dense_tc = 0;  // 64-channel nets: the dense-input forward on tcgen05 (PK_DENSE_TC; 0 = FP32-pipe kernel, measured faster so far)
   int dense_warps = 16;  // warps per CTA of the dense-input forward (PK_DENSE_WARPS; kernel iteration only)
   int zero_copy = 1;  // host-buffer calls: kernels read / write pinned host buffers directly (PK_ZERO_COPY)
   int peer_timeout_ms = 30000;  // pk_peer_clamp_adam: how long a rank waits for its peers' gradients (PK_PEER_TIMEOUT_MS)
@@ -139,6 +141,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.wide_tma_store = env_int("PK_WIDE_TMA_STORE", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   g.decide_tc = env_int("PK_DECIDE_TC", 0, 0, 2);
+  g.dense_tc = env_int("PK_DENSE_TC", 0, 0, 1);
   return PK_OK;
 }
 
@@ -157,6 +160,10 @@ extern "C" int pk_set_overlap_launches(int on) {
 }
 extern "C" int pk_debug_set_hidden_tc(int on) {
   g.hidden_tc = on ? 1 : 0;
+  return PK_OK;
+}
+extern "C" int pk_debug_set_dense_tc(int on) {
+  g.dense_tc = on ? 1 : 0;
   return PK_OK;
 }
 extern "C" int pk_debug_set_decide_tc(int mode) {
@@ -197,6 +204,10 @@ static int pk_prepare_impl(const pk_mlp* m, float* prepared, cudaStream_t st) {
       pk_pad2d_kernel<<<(unsigned)(((long long)HP * HP + T - 1) / T), T, 0, st>>>(m->w[l], prepared + lay.wn[l], H, H, HP);
     if (l > 0 && lay.tc[l])  // tcgen05 operand tiles (hi / lo, swizzled) for pk_decide_tc_kernel
       pk_tc_tiles_kernel<<<(64 * 64 + T - 1) / T, T, 0, st>>>(m->w[l], prepared + lay.tc[l], H, H);
+    if (l == 0 && lay.tc0) {  // layer 0 as tcgen05 operand tiles for pk_dense_tc_kernel
+      const int nkb = (cin + 31) >> 5;
+      pk_tc0_tiles_kernel<<<(64 * 32 * nkb + T - 1) / T, T, 0, st>>>(m->w[0], prepared + lay.tc0, H, cin, nkb);
+    }
   }
   PK_REQUIRE(m->w_out != nullptr && m->b_out != nullptr, "pk_mlp_prepare: null output tensor");
   pk_copy_pad_kernel<<<(HP + T - 1) / T, T, 0, st>>>(m->w_out, prepared + lay.wout, H, HP);
@@ -442,6 +453,21 @@ extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channel
   PK_REQUIRE(aligned16(prepared), "prepared weights must be 16-byte aligned");
   PK_REQUIRE(n_layers >= 1 && n_layers <= PK_MAX_LAYERS && n_channels >= 1 && in_channels >= 1, "bad network shape");
   const PkLayout lay = pk_make_layout(n_layers, n_channels, in_channels);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (g.dense_tc && lay.tc0 && n_layers >= 2) {
+    // 64-channel networks: every layer on the tensor cores (pk_dense_tc.cuh)
+    const PkdSmemPlan plan = pkd_smem_plan(lay, A, (unsigned)g.max_smem);
+    if (plan.x_stages >= 2) {
+      int rc = pk_set_smem(pk_dense_tc_kernel, plan.total);
+      if (rc) return rc;
+      const int nb = pkd_battles_per_tile(A), ntiles = (B + nb - 1) / nb;
+      const int tgrid = ntiles < g.sm_count ? ntiles : g.sm_count;
+      pk_dense_tc_kernel<<<tgrid, PKD_WARPS * 32, plan.total, st>>>(feat, B, A, prepared, lay, q, (unsigned)g.max_smem,
+                                                                    g.trace);
+      PK_CUDA(cudaGetLastError());
+      return PK_OK;
+    }
+  }
   const int CPL = lay.HP / 32, AT = pk_at_for(A);
   const unsigned tail_bytes = (lay.total - lay.b[0]) * 4u;
   const unsigned per_warp = ((unsigned)AT * lay.HP + PK_DENSE_DEPTH * 32u * PK_DENSE_XS(AT)) * 4u;
@@ -455,7 +481,6 @@ extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channel
   const unsigned smem = tail_bytes + per_warp * nwarps + (unsigned)cache_rows * lay.HP * 4u;
   int grid = (B + nwarps - 1) / nwarps;
   if (grid > g.sm_count) grid = g.sm_count;
-  cudaStream_t st = (cudaStream_t)stream;
 #define PK_LAUNCH_DENSE(C_, A_)                                                                  \
   {                                                                                              \
     int rc_ = pk_set_smem(pk_dense_forward_kernel<C_, A_>, smem);                                \

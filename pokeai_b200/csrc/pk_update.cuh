@@ -540,10 +540,10 @@ __global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe
     unsigned wn, tc;
     prepared[pk_flat_to_prepared(P, lay, i, &wn, &tc)] = p;
     if (wn) prepared[wn] = p;
-    if (tc) {  // tensor-core operand tiles of pk_decide_tc_kernel: hi = tf32(p), lo = p - hi
+    if (tc) {  // tensor-core operand tiles (pk_decide_tc_kernel, pk_dense_tc_kernel): hi = tf32(p), lo = p - hi
       const float hi = pk_tf32_hi(p);
       prepared[tc] = hi;
-      prepared[tc + PK_TC_TILE_FLOATS] = p - hi;
+      prepared[tc + pk_tc_lo_delta(lay, tc)] = p - hi;
     }
   }
 }
@@ -572,10 +572,10 @@ __global__ void pk_clamp_adam_kernel(float* __restrict__ params, const float* __
     unsigned wn, tc;
     prepared[pk_flat_to_prepared(P, lay, i, &wn, &tc)] = p;
     if (wn) prepared[wn] = p;
-    if (tc) {  // tensor-core operand tiles of pk_decide_tc_kernel: hi = tf32(p), lo = p - hi
+    if (tc) {  // tensor-core operand tiles (pk_decide_tc_kernel, pk_dense_tc_kernel): hi = tf32(p), lo = p - hi
       const float hi = pk_tf32_hi(p);
       prepared[tc] = hi;
-      prepared[tc + PK_TC_TILE_FLOATS] = p - hi;
+      prepared[tc + pk_tc_lo_delta(lay, tc)] = p - hi;
     }
   }
 }

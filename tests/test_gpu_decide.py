@@ -333,6 +333,47 @@ def test_dense_forward_on_arbitrary_dense_input(tables, dev):
     np.testing.assert_allclose(q.cpu().numpy(), qo, rtol=1e-4, atol=1e-4)
 
 
+@pytest.mark.parametrize("A,nl,H,B", [(9, 2, 64, 4099), (9, 2, 64, 1), (9, 2, 64, 14), (9, 2, 64, 15), (9, 3, 64, 700),
+                                      (7, 2, 48, 301), (9, 4, 64, 65), (1, 2, 64, 100), (3, 2, 64, 77), (4, 3, 33, 129),
+                                      (6, 2, 64, 2368), (8, 2, 64, 500)])
+def test_dense_forward_on_tensor_cores_matches_fp32_oracle(tables, dev, A, nl, H, B):
+    """pk_dense_tc_kernel (pk_mlp_forward for 64-channel nets under PK_DENSE_TC / pk_debug_set_dense_tc): cp.async-streamed dense blocks, operands in
+    tensor memory, every layer a tcgen05.mma.kind::tf32 contraction with a 3-term hi/lo split.  Same bar as the FP32-pipe
+    kernel (<= 1e-5 against the torch fp32 oracle, mlp_model.py:21-30) on sparse AND fully dense random input (so the lo
+    terms matter), on blocks whose address is 16-, 4- and 12-byte aligned and that end at the last byte of their view,
+    and the two kernels agree closely.  Sizes cover one battle, exactly one tile (14 at A = 9), one over, several tiles
+    per CTA."""
+    from oracle import ref_port
+    from pokeai_b200 import _native as N, ops
+    C = tables.n_channels
+    g = torch.Generator().manual_seed(1000 * A + B)
+    sd = ref_port.init_mlp_params(C, nl, H, seed=H + 3 * nl + A)
+    prepared, _, _, _ = ops.prepare_weights(sd, dev)
+    sparse = torch.randn((B, C, A), generator=g) * (torch.rand((B, C, A), generator=g) < 0.05)
+    onehot = (torch.rand((B, C, A), generator=g) < 0.03).float()
+    onehot[:, :50, :] = torch.rand((B, 50, 1), generator=g)      # ratio-valued state rows, the same in every column
+    dense = torch.rand((B, C, A), generator=g) - 0.5
+    for name, x in (("sparse", sparse), ("onehot", onehot), ("dense", dense)):
+        with torch.no_grad():
+            qo = ref_port.mlp_forward(sd, x).numpy()
+        tol = dict(rtol=Q_RTOL, atol=Q_ATOL * max(1.0, float(np.abs(qo).max())))
+        flat = torch.empty(B * C * A + 3, dtype=torch.float32, device=dev)
+        qs = {}
+        try:
+            for tc in (1, 0):
+                N.check(N.lib().pk_debug_set_dense_tc(tc))
+                for off in (0, 1, 3):   # element offsets: 16-, 4- and 12-byte aligned blocks
+                    xv = flat[off:off + B * C * A].view(B, C, A)
+                    xv.copy_(x)
+                    qg = ops.mlp_forward(prepared, nl, H, xv).cpu().numpy()
+                    np.testing.assert_allclose(qg, qo, err_msg=f"{name} tc={tc} off={off}", **tol)
+                    qs[(tc, off)] = qg
+        finally:
+            N.check(N.lib().pk_debug_set_dense_tc(0))
+        assert np.array_equal(qs[(1, 0)], qs[(1, 1)]) and np.array_equal(qs[(1, 0)], qs[(1, 3)]), name
+        assert np.abs(qs[(1, 0)] - qs[(0, 0)]).max() <= 2 * tol["atol"], name
+
+
 # ---------------------------------------------------------------------------------------------
 # select
 # ---------------------------------------------------------------------------------------------

@@ -26,9 +26,12 @@ def test_layout_sizes():
     # 43 777 parameters for the default network
     assert lib.pk_mlp_param_floats(2, 64, 617) == 43777
     assert lib.pk_mlp_param_floats(4, 2048, 617) == 13856769
-    # + the hidden matrix once more as tcgen05 operand tiles (hi / lo, 64 x 64 each) when the padded width is 64
-    assert lib.pk_mlp_prepared_floats(2, 64, 617) == (617 + 1) * 64 + 64 + 64 * 64 + 64 + 64 + 4 + 64 * 64 + 2 * 64 * 64
-    assert lib.pk_mlp_prepared_floats(3, 48, 617) == 618 * 64 + 64 + 2 * (64 * 64 + 64) + 64 + 4 + 2 * 64 * 64 + 4 * 64 * 64
+    # + the hidden matrix once more as tcgen05 operand tiles (hi / lo, 64 x 64 each) when the padded width is 64, and
+    # layer 0 as 20 k-block tiles of 128 rows x 32 floats (hi rows, lo rows)
+    tc0 = 20 * 128 * 32
+    assert lib.pk_mlp_prepared_floats(2, 64, 617) == (617 + 1) * 64 + 64 + 64 * 64 + 64 + 64 + 4 + 64 * 64 + 2 * 64 * 64 + tc0
+    assert lib.pk_mlp_prepared_floats(3, 48, 617) == (618 * 64 + 64 + 2 * (64 * 64 + 64) + 64 + 4 + 2 * 64 * 64 + 4 * 64 * 64
+                                                      + tc0)
     assert lib.pk_mlp_prepared_floats(3, 16, 617) == 618 * 32 + 32 + 2 * (32 * 32 + 32) + 32 + 4 + 2 * 32 * 32
     assert lib.pk_mlp_prepared_floats(0, 64, 617) == 0
 

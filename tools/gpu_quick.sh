@@ -1,16 +1,8 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-echo "== pytest wide"; timeout 600 python -m pytest tests/test_gpu_wide.py -m gpu -x -q 2>&1 | tail -2
-echo "== bench wide legs"; timeout 600 python bench.py --steps 5 --warmup 3 --cpu-seconds 0 --no-e2e --skip-legs shard65536,update,gpu_reference,concurrent64 | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1])
-for r in d['roofline']['secondary']: print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','per_s','transitions_per_s','ms_per_step','frac_burst','frac_sustained','error')})"
-echo "== ncu wide launches"; timeout 600 ncu --metrics gpu__time_duration.sum,sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active --clock-control none -k regex:pk_wide_gemm -c 40 --csv --log-file gpurun_out/r02_launches_wide.csv python bench_wide.py --steps 2 --warmup 3 --cpu-seconds 0 --mode train > /dev/null 2>&1
-python - <<'PY'
-import csv,collections
-rows=[r for r in csv.reader(open('gpurun_out/r02_launches_wide.csv')) if len(r)>10 and r[0].isdigit()]
-d=collections.OrderedDict()
-for r in rows: d.setdefault((r[0]),{})[r[-3]]=r[-1]
-for k,v in list(d.items())[-14:]: print(k, v)
-PY
+echo "== pytest dense tc"; timeout 300 python -m pytest tests/test_gpu_decide.py -m gpu -x -q -k "dense" 2>&1 | tail -15
+for B in 4096 65536; do for TC in 1 0; do
+echo "== quick B=$B PK_DENSE_TC=$TC"; B=$B PK_DENSE_TC=$TC timeout 120 python tools/quick_time.py 2>&1 | grep "^dense\|^B="
+done; done
+B=65536 IT0=44 IT1=64 timeout 120 python tools/trace_dense.py 2>&1 | tail -60
