@@ -165,8 +165,8 @@ PK_API int pk_debug_set_pairing(int mode);
  * dependent K = 8 MMAs per layer are latency-bound at this size and the shared memory they need takes the L1 the
  * layer-0 gathers live in -- so it is off by default. */
 PK_API int pk_debug_set_decide_tc(int mode);
-/* Tuning / test aid for pk_mlp_forward (dense input): 1 (PK_DENSE_TC in the environment; default 0) runs 64-channel
- * networks with two or more layers on the tensor cores (pk_dense_tc.cuh: cp.async-streamed blocks, operands in tensor
+/* Tuning / test aid for pk_mlp_forward (dense input): 1 (default; PK_DENSE_TC in the environment) runs 64-channel
+ * networks with two or more layers on the tensor cores (pk_dense_tc.cuh: TMA-streamed blocks, operands in tensor
  * memory, every layer a tcgen05.mma.kind::tf32 contraction with a 3-term hi/lo split, fp32-accurate); 0 keeps the
  * FP32-pipe kernel that other shapes use.  Same results up to fp32 summation order; covered by the same parity tests. */
 PK_API int pk_debug_set_dense_tc(int on);

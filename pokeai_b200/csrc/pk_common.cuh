@@ -59,7 +59,7 @@ struct PkDeviceTables {
 //                  layout (pk_tc_tile_off), so pk_decide_tc_kernel stages them with one TMA bulk load
 //   tc0 (HP == 64 only): W0 for pk_dense_tc_kernel -- per k-block of 32 input rows one 128-row K-major SWIZZLE_128B tile,
 //                  rows 0-63 = tf32(W0[j][k]), rows 64-127 = the remainders (hi element + PK_TC0_LO_DELTA), zero padded
-//                  beyond C and H; ceil(C / 32) tiles of PK_TC_TILE_FLOATS                            <- `total_all`
+//                  beyond C and H; 2 ceil(C / 64) tiles of PK_TC_TILE_FLOATS                            <- `total_all`
 #define PK_TC_TILE_FLOATS 4096u
 #define PK_TC0_LO_DELTA 2048u  // 64 rows of 32 floats
 struct PkLayout {
@@ -133,7 +133,7 @@ __host__ __device__ inline PkLayout pk_make_layout(int n_layers, int H, int C) {
   L.tc0 = 0;
   if (L.HP == 64) {
     L.tc0 = o;
-    o += (unsigned)((C + 31) >> 5) * PK_TC_TILE_FLOATS;
+    o += (unsigned)((C + 63) >> 6) * 2u * PK_TC_TILE_FLOATS;  // whole 64-row k-blocks
   }
   L.total_all = o;
   return L;

@@ -9,13 +9,16 @@
 //   tile       nb = 128 / A consecutive battles = nb * A accumulator rows (126 at A = 9); row r = (battle r / A,
 //              action column r % A), which is also the flat index of q -- the result store is one coalesced run.
 //   X stream   a battle's k-block (32 feature rows x A columns) is 128 A contiguous bytes at a 4-byte-aligned address.
-//              Warp w copies the 16-byte-aligned cover of the pieces of battles w, w + 16 with 16-byte cp.async into a
-//              ring of X stages, XS - 1 k-blocks ahead of use; completion is counted on an mbarrier
-//              (cp.async.mbarrier.arrive.noinc).  Nothing is read twice.
+//              A k-block is 64 feature rows.  Lane i of the X producer warp copies the 16-byte-aligned cover of battle
+//              i's piece (2.3 KB) with one TMA bulk load into a ring of X stages; completion is counted in bytes on an
+//              mbarrier.  Measured (tools/micro/bulk_load_bw.cu): a bulk load occupies the SM's TMA unit for ~75 cycles
+//              whatever its size, so 32-row pieces (1.2 KB) capped the stream at 4.4 TB/s chip-wide and made every
+//              issuing thread wait its turn; 16-byte cp.async (a thousand requests per k-block) was slower still.
+//              Nothing is read twice.
 //   A operand  lives in TENSOR MEMORY, not shared memory (tcgen05.mma with A from TMEM): accumulator row r is TMEM
 //              lane r, and thread (lane quarter q = warp % 4, lane t) owns row 32 q + t.  The four warps of a quarter
-//              split the k-block's 32 feature rows: warp group cg = warp / 4 reads X[row][8 cg .. 8 cg + 7] -- eight
-//              LDS whose lanes walk consecutive words -- splits them and writes 8 hi + 8 lo columns with one
+//              split the k-block's 64 feature rows: warp group cg = warp / 4 reads X[row][16 cg .. 16 cg + 15] -- sixteen
+//              LDS whose lanes walk consecutive words -- splits them and writes 16 hi + 16 lo columns with two
 //              tcgen05.st.  No transposed copy in shared memory and no proxy fence: the shared-memory pipe, which bound
 //              the first version of this kernel (A tiles in shared memory: 136 KB of traffic per 16 KB k-block), carries
 //              the X stream once in and once out, and W0.  When every lo of a k-block is zero (one-hot rows are exact
@@ -29,25 +32,30 @@
 //              TMEM; the hidden MMAs read the hidden matrices (PkLayout::tc) from shared memory; the head is a 16-channel
 //              partial dot product per thread, summed in a fixed order through shared memory.
 //
-// Tensor memory (512 columns): layer-0 accumulator 128, hidden accumulator 64, hidden A operand 128, A stages 3 x 64.
+// Tensor memory (512 columns): layer-0 accumulator 128, hidden accumulator 64, A stages 2 x 128 (the hidden layers' A
+// operand aliases stage 0).
 // Reference semantics: MLPModel.forward mlp_model.py:21-30 on Agent._calc_q_vector[_batch] input (agent.py:23-30).
 #pragma once
 
 #include "pk_decide_tc.cuh"
 
 #define PKD_TW 16                   // loading / splitting / epilogue warps
-#define PKD_PRODUCER PKD_TW         // warp index of the TMA producer (W0 stream)
-#define PKD_MMA (PKD_TW + 1)        // warp index of the MMA issuer
-#define PKD_WARPS (PKD_TW + 2)
-#define PKD_A_STAGES 3
-#define PKD_W_STAGE 16384u          // [W0 hi ; W0 lo] of one k-block: 128 rows x 128 B
-#define PKD_W_STAGES 3
-#define PKD_X_STAGES_MAX 8
+#define PKD_PRODUCER PKD_TW         // warp index of the TMA producer of the W0 stream (and the one-off weights)
+#define PKD_XPRODUCER (PKD_TW + 1)  // warp index of the TMA producer of the X stream: lane i copies battle i's piece
+#define PKD_MMA (PKD_TW + 2)        // warp index of the MMA issuer
+#define PKD_WARPS (PKD_TW + 3)
+#define PKD_KBF 64                  // feature rows per k-block: a TMA bulk load costs ~75 cycles of the SM's TMA unit
+                                    // whatever its size (tools/micro/bulk_load_bw.cu), so pieces must be >= 2 KB
+#define PKD_A_STAGES 2
+#define PKD_W_TILE 16384u           // [W0 hi ; W0 lo] of 32 input rows: 128 rows x 128 B (one PkLayout::tc0 tile)
+#define PKD_W_STAGE 32768u          // one k-block: two tiles
+#define PKD_W_STAGES 2
+#define PKD_X_STAGES_MAX 4
 #define PKD_TMEM_COLS 512u
 #define PKD_COL_ACC0 0u             // layer-0 accumulator: X_hi W_hi + X_lo W_hi | X_hi W_lo
 #define PKD_COL_HACC 128u           // hidden-layer accumulator
-#define PKD_COL_HA 192u             // hidden A operand: per K-step of 8: hi (8 columns), lo (8 columns)
-#define PKD_COL_A 320u              // A stages, 64 columns each, same K-step layout
+#define PKD_COL_A 192u              // A stages, 128 columns each: per K-step of 8: hi (8 columns), lo (8 columns)
+#define PKD_COL_HA PKD_COL_A        // hidden A operand (same K-step layout): aliases A stage 0, idle during the epilogue
 
 struct PkdSmemPlan {
   unsigned w;         // W0 k-block stages
@@ -82,7 +90,7 @@ __host__ __device__ inline PkdSmemPlan pkd_smem_plan(const PkLayout& lay, int A,
   o += 8u * (2u * PKD_X_STAGES_MAX + 2u * PKD_A_STAGES + 2u * PKD_W_STAGES + 4u) + 16u;
   o = (o + 127u) & ~127u;
   p.x = o;
-  p.piece = 128u * (unsigned)A + 32u;  // the aligned cover of 128 A bytes at any 4-byte alignment
+  p.piece = 4u * PKD_KBF * (unsigned)A + 32u;  // the aligned cover of a k-block's bytes at any 4-byte alignment
   p.x_stage = (nb * p.piece + 127u) & ~127u;
   const unsigned room = max_smem > o + 1024u ? max_smem - o - 1024u : 0u;
   p.x_stages = room / p.x_stage;
@@ -125,18 +133,22 @@ __device__ __forceinline__ void pkd_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uin
 }
 
 // sixteen values of one row -> two K-steps of an A operand in TMEM: per K-step hi (8 columns) then lo (8 columns)
-__device__ __forceinline__ void pkd_split_store16(uint32_t taddr, const float (&x)[16]) {
+// Returns the OR of the lo bit patterns.
+__device__ __forceinline__ uint32_t pkd_split_store16(uint32_t taddr, const float (&x)[16]) {
+  uint32_t lo_or = 0u;
 #pragma unroll
   for (int s = 0; s < 2; ++s) {
     uint32_t v[16];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float hi = pk_tf32_hi(x[8 * s + j]);
+      const float hi = pk_tf32_hi(x[8 * s + j]), lo = x[8 * s + j] - hi;
       v[j] = __float_as_uint(hi);
-      v[8 + j] = __float_as_uint(x[8 * s + j] - hi);
+      v[8 + j] = __float_as_uint(lo);
+      lo_or |= __float_as_uint(lo);
     }
     pkd_tmem_st16(taddr + 16u * (uint32_t)s, v);
   }
+  return lo_or;
 }
 
 // debug timeline (pk_debug_set_trace): SM clock of CTA 0 at point p of iteration it < 128 of role 0 (warp 0),
@@ -156,7 +168,7 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
   const int XS = (int)plan.x_stages;
   const int nb = pkd_battles_per_tile(A), rows = nb * A;
   const int L = lay.C * A;
-  const int NKB = (lay.C + 31) >> 5;
+  const int NKB = (lay.C + PKD_KBF - 1) / PKD_KBF;
   const int ntiles = (B + nb - 1) / nb;
   const int n_hidden = lay.n_layers - 1;  // >= 1
 
@@ -180,7 +192,7 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < PKD_X_STAGES_MAX; ++i) {
-      pk_mbar_init(x_full + i, PKD_TW * 32);  // every copying thread (cp.async.mbarrier.arrive.noinc)
+      pk_mbar_init(x_full + i, 1);  // the producer's arrive.expect_tx with the byte count of the stage's copies
       pk_mbar_init(x_empty + i, PKD_TW);
     }
     for (int i = 0; i < PKD_A_STAGES; ++i) {
@@ -229,6 +241,48 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
       }
     }
     __syncwarp();
+  } else if (warp == PKD_XPRODUCER) {
+    // ---- TMA producer of the X stream: lane i < nb copies the 16-byte-aligned cover of battle i's k-block ----
+    const unsigned long long feat_addr = (unsigned long long)feat;
+    const unsigned long long arr_end16 = (feat_addr + (unsigned long long)B * L * 4ull) & ~15ull;
+    uint32_t xit = 0;
+    unsigned long long* ptr = (blockIdx.x == 0 && lane == 0) ? trace : nullptr;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long b = (long long)tile * nb + lane;
+      const bool mine = lane < nb && b < B;
+      for (int kb = 0; kb < NKB; ++kb, ++xit) {
+        const int xs = (int)(xit % (uint32_t)XS);
+        pkd_trace(ptr, 2, xit, 2);
+        pk_mbar_wait(x_empty + xs, ((xit / (uint32_t)XS) & 1u) ^ 1u);
+        pkd_trace(ptr, 2, xit, 3);
+        uint32_t bytes = 0;
+        unsigned long long src = 0;
+        unsigned char* dst = smem + plan.x + (unsigned)xs * plan.x_stage + (unsigned)lane * plan.piece;
+        if (mine) {
+          const unsigned long long addr =
+              feat_addr + 4ull * ((unsigned long long)b * L + (unsigned long long)kb * PKD_KBF * A);
+          const uint32_t mis = (uint32_t)(addr & 15ull);
+          const uint32_t len = (uint32_t)min(PKD_KBF, lay.C - kb * PKD_KBF) * (uint32_t)A * 4u;
+          src = addr - mis;
+          bytes = (mis + len + 15u) & ~15u;
+          if (src + bytes > arr_end16) {
+            // the cover would pass the end of the array: bulk-copy the whole 16-byte chunks, the rest by hand
+            const uint32_t whole = arr_end16 > src ? (uint32_t)(arr_end16 - src) : 0u;
+            for (uint32_t o = whole > mis ? whole : mis; o < mis + len; o += 4u)
+              *reinterpret_cast<float*>(dst + o) = __ldg(reinterpret_cast<const float*>(src + o));
+            bytes = whole;
+          }
+        }
+        uint32_t total = bytes;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) total += __shfl_xor_sync(0xffffffffu, total, d);
+        __syncwarp();  // the hand-copied floats above are ordered before lane 0's arrival
+        if (lane == 0) pk_mbar_expect_tx(x_full + xs, total);
+        __syncwarp();
+        if (bytes) pk_bulk_load(dst, reinterpret_cast<const void*>(src), bytes, x_full + xs);
+        pkd_trace(ptr, 2, xit, 4);
+      }
+    }
   } else if (warp == PKD_MMA) {
     // ---- MMA issuer ----
     if (lane == 0) {
@@ -250,10 +304,10 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
           pkw_tc_fence_after();
           const uint32_t fl = lo_flag[as * 2 + (int)aph];
           lo_flag[as * 2 + (int)aph] = 0u;  // set again two uses of this stage later, after the commit below
-          const uint32_t ta = tmem_base + PKD_COL_A + 64u * (uint32_t)as, tw = w_u32 + (uint32_t)ws * PKD_W_STAGE;
+          const uint32_t ta = tmem_base + PKD_COL_A + 128u * (uint32_t)as, tw = w_u32 + (uint32_t)ws * PKD_W_STAGE;
 #pragma unroll
-          for (int s = 0; s < 4; ++s) {  // UMMA_K = 8 fp32: 16 TMEM columns (hi | lo) of A, 32 B of the swizzle atom of W
-            const uint64_t bd = pkw_smem_desc_k128(tw) + 2u * (uint64_t)s;
+          for (int s = 0; s < PKD_KBF / 8; ++s) {  // UMMA_K = 8 fp32: 16 TMEM columns (hi | lo) of A, 32 B of the swizzle atom of W
+            const uint64_t bd = pkw_smem_desc_k128(tw + (uint32_t)(s >> 2) * PKD_W_TILE) + 2u * (uint64_t)(s & 3);
             pkd_mma_ts(tmem_base + PKD_COL_ACC0, ta + 16u * (uint32_t)s, bd, idesc_hi, (kb | s) != 0 ? 1u : 0u);
             if (fl) pkd_mma_ts(tmem_base + PKD_COL_ACC0, ta + 16u * (uint32_t)s + 8u, bd, idesc_lo, 1u);
           }
@@ -295,98 +349,65 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
     const unsigned long long feat_addr = (unsigned long long)feat;
     const uint32_t tlane = tmem_base + ((uint32_t)(32 * wq) << 16);
     // element (k, ra) of this row's battle inside a stage: piece rbi, float index k * A + ra (+ the piece's misalignment)
-    const uint32_t src_row = (uint32_t)rbi * plan.piece + (uint32_t)ra * 4u + (uint32_t)(8 * cg * A) * 4u;
-    uint32_t xit = 0, ait = 0, tpar = 0, hpar = 0;
+    const uint32_t src_row = (uint32_t)rbi * plan.piece + (uint32_t)ra * 4u + (uint32_t)((PKD_KBF / 4) * cg * A) * 4u;
+    uint32_t tpar = 0, hpar = 0;
     bool first = true;
     unsigned long long* ttr = (blockIdx.x == 0 && threadIdx.x == 0) ? trace : nullptr;
-    // X copies: warp w brings in the pieces of battles w, w + 16 of a tile -- the 16-byte-aligned cover of each piece,
-    // 16 bytes per lane and cp.async -- XS - 1 k-blocks ahead of their use, across tile boundaries
-    const unsigned long long arr_end = feat_addr + (unsigned long long)B * L * 4ull;
-    uint32_t iit = 0;  // iteration the next issue is for
-    int itile = blockIdx.x, ikb = 0;
-    auto issue = [&]() {
-      if (itile < ntiles) {
-        const uint32_t sbase = x_u32 + (iit % (uint32_t)XS) * plan.x_stage;
-        const uint32_t len = (uint32_t)min(32, lay.C - ikb * 32) * (uint32_t)A * 4u;
-        for (int pb = warp; pb < nb; pb += PKD_TW) {
-          const long long b = (long long)itile * nb + pb;
-          if (b >= B) break;
-          const unsigned long long addr = feat_addr + 4ull * ((unsigned long long)b * L + (unsigned long long)ikb * 32 * A);
-          const uint32_t mis = (uint32_t)(addr & 15ull);
-          const unsigned long long src = addr - mis;
-          const uint32_t nch = (mis + len + 15u) >> 4;
-          const uint32_t dst = sbase + (uint32_t)pb * plan.piece;
-          for (uint32_t c = lane; c < nch; c += 32u) {
-            const unsigned long long g = src + 16ull * c;
-            if (g + 16ull <= arr_end) {
-              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * c), "l"(g) : "memory");
-            } else {  // the last chunk of the array: only the floats that exist
-              for (uint32_t e = 0; e < 16u && g + e + 4ull <= arr_end; e += 4u)
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 16u * c + e), "l"(g + e) : "memory");
-            }
-          }
-        }
-      }
-      // counts as this thread's arrival once its copies above have landed (immediately if it made none)
-      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(pk_smem_u32(x_full + iit % (uint32_t)XS))
-                   : "memory");
-      ++iit;
-      if (++ikb == NKB) {
-        ikb = 0;
-        itile += gridDim.x;
+    const uint32_t my_tiles = (uint32_t)((ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x);
+    const uint32_t n_it = my_tiles * (uint32_t)NKB;
+    // the loads of iteration j: this thread's sixteen X values of k-block j -> registers; then the stage is released
+    int ltile = blockIdx.x, lkb = 0;
+    uint32_t lit = 0;
+    float xn[PKD_KBF / 4];
+    auto load_x = [&]() {
+      const int xs = (int)(lit % (uint32_t)XS);
+      pk_mbar_wait(x_full + xs, (lit / (uint32_t)XS) & 1u);
+      const uint32_t mis =
+          (uint32_t)((feat_addr + 4ull * (unsigned long long)((long long)ltile * nb + rbi) * (unsigned long long)L) & 15ull);
+      const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_row + mis;
+      const int k0 = lkb * PKD_KBF + (PKD_KBF / 4) * cg;
+#pragma unroll
+      for (int j = 0; j < PKD_KBF / 4; ++j) xn[j] = (row_ok && k0 + j < lay.C) ? pkd_lds(xb + (uint32_t)(j * A) * 4u) : 0.0f;
+      __syncwarp();
+      if (lane == 0) pkw_mbar_arrive(x_empty + xs);
+      ++lit;
+      if (++lkb == NKB) {
+        lkb = 0;
+        ltile += gridDim.x;
       }
     };
-    for (int i = 0; i < XS - 1; ++i) issue();
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const long long b0 = (long long)tile * nb;
-      const uint32_t src_t =
-          src_row + (uint32_t)((feat_addr + 4ull * (unsigned long long)(b0 + rbi) * (unsigned long long)L) & 15ull);
-      for (int kb = 0; kb < NKB; ++kb, ++xit, ++ait) {
-        const int xs = (int)(xit % (uint32_t)XS);
-        const uint32_t xph = (xit / (uint32_t)XS) & 1u;
-        const int as = (int)(ait % PKD_A_STAGES);
-        const uint32_t aph = (ait / PKD_A_STAGES) & 1u;
-        pkd_trace(ttr, 0, xit, 0);
-        if (xit > 0) {  // refill the stage the previous iteration consumed (every warp has left it, or is about to)
-          const uint32_t j = xit - 1u;
-          pk_mbar_wait(x_empty + (int)(j % (uint32_t)XS), (j / (uint32_t)XS) & 1u);
-        }
-        pkd_trace(ttr, 0, xit, 1);
-        issue();
-        pkd_trace(ttr, 0, xit, 2);
-        pk_mbar_wait(x_full + xs, xph);
-        pkd_trace(ttr, 0, xit, 3);
-        const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_t;
-        const int k0 = kb * 32 + 8 * cg;
-        float x[8];
+    load_x();
+    int tile = blockIdx.x, kb = 0;
+    for (uint32_t it = 0; it < n_it; ++it) {
+      const int as = (int)(it % PKD_A_STAGES);
+      const uint32_t aph = (it / PKD_A_STAGES) & 1u;
+      float x[PKD_KBF / 4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          x[j] = (row_ok && k0 + j < lay.C) ? pkd_lds(xb + (uint32_t)(j * A) * 4u) : 0.0f;
-        __syncwarp();
-        if (lane == 0) pkw_mbar_arrive(x_empty + xs);
-        pk_mbar_wait(a_empty + as, aph ^ 1u);
-        pkw_tc_fence_after();
-        pkd_trace(ttr, 0, xit, 4);
-        uint32_t v[16];
-        uint32_t lo_or = 0u;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float hi = pk_tf32_hi(x[j]), lo = x[j] - hi;
-          v[j] = __float_as_uint(hi);
-          v[8 + j] = __float_as_uint(lo);
-          lo_or |= __float_as_uint(lo);
-        }
-        pkd_tmem_st16(tlane + PKD_COL_A + 64u * (uint32_t)as + 16u * (uint32_t)cg, v);
+      for (int j = 0; j < PKD_KBF / 4; ++j) x[j] = xn[j];
+      pkd_trace(ttr, 0, it, 0);
+      if (it + 1u < n_it) load_x();  // the next k-block's values, in flight under the split and the TMEM store below
+      pkd_trace(ttr, 0, it, 3);
+      pk_mbar_wait(a_empty + as, aph ^ 1u);
+      pkw_tc_fence_after();
+      pkd_trace(ttr, 0, it, 4);
+      {
+        static_assert(PKD_KBF == 64, "sixteen values per thread: two K-steps");
+        const uint32_t lo_or = pkd_split_store16(tlane + PKD_COL_A + 128u * (uint32_t)as + 32u * (uint32_t)cg, x);
         const bool any_lo = __any_sync(0xffffffffu, (lo_or << 1) != 0u);
         pkd_tmem_st_wait();
         pkw_tc_fence_before();
         __syncwarp();
-        pkd_trace(ttr, 0, xit, 5);
         if (lane == 0) {
           if (any_lo) lo_flag[as * 2 + (int)aph] = 1u;
           pkw_mbar_arrive(a_full + as);
         }
       }
+      pkd_trace(ttr, 0, it, 5);
+      if (++kb < NKB) continue;
+      kb = 0;
+      const long long b0 = (long long)tile * nb;
+      tile += gridDim.x;
+      const uint32_t xit = it + 1u;
       // ---- layer-0 epilogue: relu(D[:, j] + D[:, 64 + j] + b0[j]) -> the hidden layer's A operand (TMEM) ----
       pkd_trace(ttr, 0, xit - 1u, 6);
       pk_mbar_wait(acc0_full, tpar);

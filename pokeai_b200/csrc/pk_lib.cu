@@ -55,7 +55,7 @@ struct PkGlobal {
   // sessions, whose records always arrive from host memory (PK_PDL_SESSION=0 turns that off)
   int pdl = 0;
   int pdl_session = 1;
-  int dense_tc = 0;  // 64-channel nets: the dense-input forward on tcgen05 (PK_DENSE_TC; 0 = FP32-pipe kernel, measured faster so far)
+  int dense_tc = 1;  // 64-channel nets: the dense-input forward on tcgen05 (PK_DENSE_TC; 0 = FP32-pipe kernel)
   int dense_warps = 16;  // warps per CTA of the dense-input forward (PK_DENSE_WARPS; kernel iteration only)
   int zero_copy = 1;  // host-buffer calls: kernels read / write pinned host buffers directly (PK_ZERO_COPY)
   int peer_timeout_ms = 30000;  // pk_peer_clamp_adam: how long a rank waits for its peers' gradients (PK_PEER_TIMEOUT_MS)
@@ -141,7 +141,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.wide_tma_store = env_int("PK_WIDE_TMA_STORE", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   g.decide_tc = env_int("PK_DECIDE_TC", 0, 0, 2);
-  g.dense_tc = env_int("PK_DENSE_TC", 0, 0, 1);
+  g.dense_tc = env_int("PK_DENSE_TC", 1, 0, 1);
   return PK_OK;
 }
 
@@ -205,7 +205,7 @@ static int pk_prepare_impl(const pk_mlp* m, float* prepared, cudaStream_t st) {
     if (l > 0 && lay.tc[l])  // tcgen05 operand tiles (hi / lo, swizzled) for pk_decide_tc_kernel
       pk_tc_tiles_kernel<<<(64 * 64 + T - 1) / T, T, 0, st>>>(m->w[l], prepared + lay.tc[l], H, H);
     if (l == 0 && lay.tc0) {  // layer 0 as tcgen05 operand tiles for pk_dense_tc_kernel
-      const int nkb = (cin + 31) >> 5;
+      const int nkb = ((cin + 63) >> 6) * 2;
       pk_tc0_tiles_kernel<<<(64 * 32 * nkb + T - 1) / T, T, 0, st>>>(m->w[0], prepared + lay.tc0, H, cin, nkb);
     }
   }

@@ -337,7 +337,7 @@ def test_dense_forward_on_arbitrary_dense_input(tables, dev):
                                       (7, 2, 48, 301), (9, 4, 64, 65), (1, 2, 64, 100), (3, 2, 64, 77), (4, 3, 33, 129),
                                       (6, 2, 64, 2368), (8, 2, 64, 500)])
 def test_dense_forward_on_tensor_cores_matches_fp32_oracle(tables, dev, A, nl, H, B):
-    """pk_dense_tc_kernel (pk_mlp_forward for 64-channel nets under PK_DENSE_TC / pk_debug_set_dense_tc): cp.async-streamed dense blocks, operands in
+    """pk_dense_tc_kernel (pk_mlp_forward's default for 64-channel nets): TMA-streamed dense blocks, operands in
     tensor memory, every layer a tcgen05.mma.kind::tf32 contraction with a 3-term hi/lo split.  Same bar as the FP32-pipe
     kernel (<= 1e-5 against the torch fp32 oracle, mlp_model.py:21-30) on sparse AND fully dense random input (so the lo
     terms matter), on blocks whose address is 16-, 4- and 12-byte aligned and that end at the last byte of their view,
@@ -369,7 +369,7 @@ def test_dense_forward_on_tensor_cores_matches_fp32_oracle(tables, dev, A, nl, H
                     np.testing.assert_allclose(qg, qo, err_msg=f"{name} tc={tc} off={off}", **tol)
                     qs[(tc, off)] = qg
         finally:
-            N.check(N.lib().pk_debug_set_dense_tc(0))
+            N.check(N.lib().pk_debug_set_dense_tc(1))
         assert np.array_equal(qs[(1, 0)], qs[(1, 1)]) and np.array_equal(qs[(1, 0)], qs[(1, 3)]), name
         assert np.abs(qs[(1, 0)] - qs[(0, 0)]).max() <= 2 * tol["atol"], name
 

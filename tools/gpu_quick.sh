@@ -5,4 +5,4 @@ echo "== pytest dense tc"; timeout 300 python -m pytest tests/test_gpu_decide.py
 for B in 4096 65536; do for TC in 1 0; do
 echo "== quick B=$B PK_DENSE_TC=$TC"; B=$B PK_DENSE_TC=$TC timeout 120 python tools/quick_time.py 2>&1 | grep "^dense\|^B="
 done; done
-B=65536 IT0=44 IT1=64 timeout 120 python tools/trace_dense.py 2>&1 | tail -60
+PK_DENSE_TC=1 B=65536 timeout 120 python tools/trace_dense.py 2>&1 | tail -60

@@ -31,10 +31,10 @@ torch.cuda.synchronize()
 N.check(N.lib().pk_debug_set_trace(None))
 t = tr.cpu().numpy()
 t0 = t[t > 0].min()
-roles = {0: ["top", "x_empty", "issued", "x_full", "lds+a_empty", "tmem st", "(tile end) loop out", "(tile end) head done"],
+roles = {0: ["top", "-", "-", "next lds", "a_empty", "tmem st", "(tile end) loop out", "(tile end) head done"],
          1: ["top", "a_full", "w_full", "issued", "committed"],
-         2: ["top", "w_empty"]}
-lo, hi = int(os.environ.get("IT0", 40)), int(os.environ.get("IT1", 64))
+         2: ["W top", "w_empty", "X top", "x_empty", "x issued"]}
+lo, hi = int(os.environ.get("IT0", 20)), int(os.environ.get("IT1", 44))
 for r, names in roles.items():
     print(f"role {r}: cycles since kernel start at each point, iterations {lo}..{hi - 1}")
     print("   it " + " ".join(f"{n:>10s}" for n in names))
