@@ -14,6 +14,8 @@ calls `run_all()`, which runs bounded legs (about a minute in total) whose resul
   configs[4]  wide 4 x 2048 net, forward and forward + backward on the tensor cores; fractions of the burst AND the
               sustained measured bf16 peak
   configs[0]  64 concurrent battles through the lock-step driver (latency per decision round)
+  dense       pk_mlp_forward on pre-encoded dense features (what agent.py:28-30 / party_evaluator_quick.py:101 hand in):
+              65 536 states, HBM-bound by the 22 212 B + 36 B per decision it reads and writes
   gpu_reference  the reference's own GPU path (party_evaluator_quick.py:93-104): MLPModel in eager PyTorch on cuda on
               PRE-ENCODED dense features + mask + argmax, default and wide net -- the GPU bar SURVEY.md 2.2 names.
 
@@ -102,6 +104,35 @@ def leg_shard65536(ctx, total=65536, steps=10):
                       "features+mask+Q+action written", "scaling": "strong", "decisions_per_s": B * world / (ms * 1e-3),
             "launch_us": ms * 1e3, "steps": steps, "roofline_bound": "hbm", "achieved_gbs_per_gpu": ach,
             "frac": ach / pk_["hbm"], "peak": pk_["hbm"], "l2": f"{n_rot} rotating output sets of {B * 617 * A * 4 / 1e6:.0f} MB"}
+
+
+# ---- dense-input forward (Agent._calc_q_vector_batch's input) -------------------------------------------------------
+def leg_dense_forward(ctx, total=65536, steps=10):
+    import torch
+    from pokeai_b200 import ops
+    from pokeai_b200.packed import synth_packed
+    dev, world, rank = ctx.dev, ctx.world, ctx.rank
+    B = total // world
+    n_rot = 2 if B * 617 * A * 4 > 126 * 1024 * 1024 else 4
+    feats = []
+    for i in range(n_rot):
+        pk = ops.packed_to_device(synth_packed(B, seed=7100 + 10 * rank + i, party_size=PARTY_SIZE, kind="full"), dev)
+        feats.append(ops.encode(pk, A)[0])
+    q = torch.empty((B, A), dtype=torch.float32, device=dev)
+
+    def step(i):
+        ops.mlp_forward(ctx.prepared, 2, 64, feats[i % n_rot], out=q)
+
+    ms = _timed(ctx, step, steps)
+    pk_ = _peaks()
+    bytes_per = 617 * A * 4 + A * 4
+    ach = bytes_per * B / (ms * 1e-3) / 1e9
+    del feats
+    return {"config": f"dense-input forward (pk_mlp_forward, tensor cores): {total} states over {world} GPU(s), {B} per launch "
+                      "per GPU, default MLP 2x64, dense (B, 617, 9) fp32 features in HBM -> Q", "scaling": "strong",
+            "decisions_per_s": B * world / (ms * 1e-3), "launch_us": ms * 1e3, "steps": steps, "roofline_bound": "hbm",
+            "bytes_per_decision": bytes_per, "achieved_gbs_per_gpu": ach, "frac": ach / pk_["hbm"], "peak": pk_["hbm"],
+            "l2": f"{n_rot} rotating input sets of {B * 617 * A * 4 / 1e6:.0f} MB"}
 
 
 # ---- configs[3]: the DQN update and its gradient exchange ---------------------------------------------------------
@@ -538,7 +569,7 @@ def leg_concurrent64(ctx, n_battles=64, rounds=200):
 
 
 def run_all(ctx, skip=()):
-    legs = [("shard65536", leg_shard65536), ("update", leg_update), ("wide", leg_wide), ("wide_update", leg_wide_update),
+    legs = [("shard65536", leg_shard65536), ("dense", leg_dense_forward), ("update", leg_update), ("wide", leg_wide), ("wide_update", leg_wide_update),
             ("gpu_reference", leg_gpu_reference), ("concurrent64", leg_concurrent64)]
     import torch
     out = []

@@ -8,32 +8,46 @@
 //
 //   tile       nb = 128 / A consecutive battles = nb * A accumulator rows (126 at A = 9); row r = (battle r / A,
 //              action column r % A), which is also the flat index of q -- the result store is one coalesced run.
-//   X stream   a battle's k-block (32 feature rows x A columns) is 128 A contiguous bytes at a 4-byte-aligned address.
-//              A k-block is 64 feature rows.  Lane i of the X producer warp copies the 16-byte-aligned cover of battle
-//              i's piece (2.3 KB) with one TMA bulk load into a ring of X stages; completion is counted in bytes on an
-//              mbarrier.  Measured (tools/micro/bulk_load_bw.cu): a bulk load occupies the SM's TMA unit for ~75 cycles
-//              whatever its size, so 32-row pieces (1.2 KB) capped the stream at 4.4 TB/s chip-wide and made every
-//              issuing thread wait its turn; 16-byte cp.async (a thousand requests per k-block) was slower still.
-//              Nothing is read twice.
+//   pairs      a CTA works on TWO tiles at a time against each W0 k-block: two accumulators, one A stage per tile, the
+//              W0 stream (as many bytes per tile as the features themselves) shared between them.
+//   X stream   a k-block is 64 feature rows: per battle 256 A contiguous bytes at a 4-byte-aligned address.  A lane of
+//              one of the two X producer warps copies the 16-byte-aligned cover of one battle's piece (2.3 KB) with a TMA
+//              bulk load into a ring of four X stages; completion is counted in bytes on an mbarrier.  Nothing is read
+//              twice.
 //   A operand  lives in TENSOR MEMORY, not shared memory (tcgen05.mma with A from TMEM): accumulator row r is TMEM
-//              lane r, and thread (lane quarter q = warp % 4, lane t) owns row 32 q + t.  The four warps of a quarter
-//              split the k-block's 64 feature rows: warp group cg = warp / 4 reads X[row][16 cg .. 16 cg + 15] -- sixteen
-//              LDS whose lanes walk consecutive words -- splits them and writes 16 hi + 16 lo columns with two
-//              tcgen05.st.  No transposed copy in shared memory and no proxy fence: the shared-memory pipe, which bound
-//              the first version of this kernel (A tiles in shared memory: 136 KB of traffic per 16 KB k-block), carries
-//              the X stream once in and once out, and W0.  When every lo of a k-block is zero (one-hot rows are exact
-//              in tf32) the lo MMA is skipped.
-//   W0         per k-block a 128-row B operand [tf32(W0) ; W0 - tf32(W0)] (16 KB, PkLayout::tc0, kept current by
-//              pk_clamp_adam), streamed from L2 with one TMA bulk load per k-block: MMA N = 128 gives X_hi W_hi in
-//              accumulator columns 0-63 and X_hi W_lo in 64-127; the N = 64 lo MMA adds X_lo W_hi to columns 0-63.
+//              lane r, and thread (lane quarter q, lane t) owns row 32 q + t.  Warps 0-7 feed tile 0 of the pair, warps
+//              8-15 tile 1, so the two sets drift apart and one set's shared-memory reads overlap the other's TMEM
+//              stores.  Within a set warp (q, half) reads X[row][32 half .. 32 half + 31] -- thirty-two LDS whose lanes
+//              walk consecutive words -- splits them and stores the hi parts (and the lo parts when there are any:
+//              one-hot rows are exact in tf32, and a group of lo columns that already holds zeros is not stored
+//              again) with tcgen05.st.  No transposed copy in shared memory and no proxy fence.
+//   W0         per k-block a 128-row B operand [tf32(W0) ; W0 - tf32(W0)] (32 KB, PkLayout::tc0, kept current by
+//              pk_clamp_adam), streamed from L2 with one TMA bulk load per k-block and pair: MMA N = 128 gives X_hi W_hi
+//              in accumulator columns 0-63 and X_hi W_lo in 64-127; the N = 64 lo MMA adds X_lo W_hi to columns 0-63.
+//              The hidden matrices (PkLayout::tc) ride the same ring during the epilogue.
 //   MMA warp   one thread issues; tcgen05.commit releases the stages.
-//   epilogue   the sixteen warps again: thread (row, cg) reads channels 16 cg .. +15 of its row from the accumulator,
-//              adds the two halves and the bias, applies ReLU, splits and writes the hidden layer's A operand -- also in
-//              TMEM; the hidden MMAs read the hidden matrices (PkLayout::tc) from shared memory; the head is a 16-channel
-//              partial dot product per thread, summed in a fixed order through shared memory.
+//   epilogue   all sixteen warps, one tile at a time: thread (row, cg) reads channels 16 cg .. +15 of its row from the
+//              accumulator, adds the two halves and the bias, applies ReLU, splits and writes the hidden layer's A
+//              operand -- also in TMEM; the head is a 16-channel partial dot product per thread, summed in a fixed
+//              order through shared memory.
+// Tensor memory (512 columns): two layer-0 accumulators of 128, A stages 2 x 128 (the hidden layers' A operand and
+// accumulator alias them during the epilogue).
 //
-// Tensor memory (512 columns): layer-0 accumulator 128, hidden accumulator 64, A stages 2 x 128 (the hidden layers' A
-// operand aliases stage 0).
+// Measured on B200, 65 536 states: 375 - 395 us = 0.57 - 0.60 of the HBM roofline (FP32-pipe kernel:
+// 569 us, 0.39); 4 096 states 31 - 33 us (54).  What was learned on the way, each from a timeline of the roles
+// (tools/trace_dense.py) or a microbenchmark (tools/micro/bulk_load_bw.cu):
+//   * A tiles in SHARED memory (transposed by LDS + STS): 136 KB of shared-memory traffic per 16 KB of input -- the
+//     shared-memory pipe bound the kernel at 700 us.
+//   * a TMA bulk load occupies the SM's TMA unit for ~75 cycles whatever its size (592 B .. 2.4 KB: 2.2 / 4.4 / 9.3 TB/s
+//     chip-wide from L2); 32-row pieces (1.2 KB) capped the stream and every issuing thread waited its turn (840 us);
+//     16-byte cp.async, a thousand requests per k-block, stalled the issuing warps (960 us).  64-row pieces: 414 us.
+//     One warp issues its lanes' bulk loads ~115 cycles apart; two producer warps reach the unit's 75.
+//   * a tcgen05.mma whose A operand is in TMEM issues every ~131 - 150 cycles whatever its N (64 or 128), whether
+//     successive MMAs share an accumulator or alternate between two; two issuing warps are slower (~200).  Eight per
+//     tile and k-block = ~1 200 cycles: with the X producer (~1 400 per k-block with its waits) this is what bounds
+//     the kernel now.  Without the MMAs the kernel takes 320 us, without MMAs and TMEM stores 311 us.
+//   * next: X through tensor maps (four boxes per k-block instead of fourteen bulk loads) and layer 0 as bf16 x 3-way
+//     split with K = 16 per MMA (half the MMAs); neither is built.
 // Reference semantics: MLPModel.forward mlp_model.py:21-30 on Agent._calc_q_vector[_batch] input (agent.py:23-30).
 #pragma once
 
@@ -41,9 +55,11 @@
 
 #define PKD_TW 16                   // loading / splitting / epilogue warps
 #define PKD_PRODUCER PKD_TW         // warp index of the TMA producer of the W0 stream (and the one-off weights)
-#define PKD_XPRODUCER (PKD_TW + 1)  // warp index of the TMA producer of the X stream: lane i copies battle i's piece
-#define PKD_MMA (PKD_TW + 2)        // warp index of the MMA issuer
-#define PKD_WARPS (PKD_TW + 3)
+#define PKD_XPRODUCER (PKD_TW + 1)  // first warp of the TMA producers of the X stream
+#define PKD_XPW 2                   // X producer warps: lane i of warp j copies the piece of battle PKD_XPW i + j (a warp issues
+                                    // its lanes' bulk loads one after the other, ~115 cycles each: two warps keep the TMA unit fed)
+#define PKD_MMA (PKD_TW + 1 + PKD_XPW)  // warp index of the MMA issuer
+#define PKD_WARPS (PKD_TW + 2 + PKD_XPW)
 #define PKD_KBF 64                  // feature rows per k-block: a TMA bulk load costs ~75 cycles of the SM's TMA unit
                                     // whatever its size (tools/micro/bulk_load_bw.cu), so pieces must be >= 2 KB
 #define PKD_A_STAGES 2
@@ -52,14 +68,14 @@
 #define PKD_W_STAGES 2
 #define PKD_X_STAGES_MAX 4
 #define PKD_TMEM_COLS 512u
-#define PKD_COL_ACC0 0u             // layer-0 accumulator: X_hi W_hi + X_lo W_hi | X_hi W_lo
-#define PKD_COL_HACC 128u           // hidden-layer accumulator
-#define PKD_COL_A 192u              // A stages, 128 columns each: per K-step of 8: hi (8 columns), lo (8 columns)
-#define PKD_COL_HA PKD_COL_A        // hidden A operand (same K-step layout): aliases A stage 0, idle during the epilogue
+#define PKD_COL_ACC0 0u             // layer-0 accumulators of the pair's two tiles, 128 columns each:
+                                    // X_hi W_hi + X_lo W_hi | X_hi W_lo
+#define PKD_COL_A 256u              // A stages (one per tile of the pair), 128 columns each: hi parts (64, column = k), lo parts (64)
+#define PKD_COL_HA PKD_COL_A        // hidden A operand (per K-step of 8: hi (8), lo (8)): aliases A stage 0, idle during the epilogue
+#define PKD_COL_HACC (PKD_COL_A + 128u)  // hidden-layer accumulator (64 columns): aliases the hi half of A stage 1
 
 struct PkdSmemPlan {
-  unsigned w;         // W0 k-block stages
-  unsigned w1;        // hidden matrices as B operands (PkLayout::tc), PKT_SET_BYTES each
+  unsigned w;         // W stages: W0 k-blocks, and the hidden matrices (PkLayout::tc, one stage each) during the epilogue
   unsigned x;         // X stages
   unsigned x_stage, x_stages, piece;  // bytes per stage, stages, bytes per battle slot
   unsigned small;     // b[0..n_layers-1], wout, bout
@@ -78,8 +94,6 @@ __host__ __device__ inline PkdSmemPlan pkd_smem_plan(const PkLayout& lay, int A,
   unsigned o = 0;
   p.w = o;
   o += PKD_W_STAGE * PKD_W_STAGES;
-  p.w1 = o;
-  o += PKT_SET_BYTES * (unsigned)(lay.n_layers - 1);
   p.small = o;
   o += ((unsigned)lay.n_layers * PKT_H + PKT_H + 4u) * 4u;
   p.part = o;
@@ -171,6 +185,7 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
   const int NKB = (lay.C + PKD_KBF - 1) / PKD_KBF;
   const int ntiles = (B + nb - 1) / nb;
   const int n_hidden = lay.n_layers - 1;  // >= 1
+  const int npairs = (ntiles + 1) >> 1;
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + plan.bars);
   uint64_t* x_full = bars;
@@ -187,16 +202,16 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
   volatile uint32_t* lo_flag = reinterpret_cast<volatile uint32_t*>(smem + plan.flags);  // [A stage][phase]
   float* s_small = reinterpret_cast<float*>(smem + plan.small);
   float* s_part = reinterpret_cast<float*>(smem + plan.part);
-  const uint32_t w_u32 = pk_smem_u32(smem + plan.w), w1_u32 = pk_smem_u32(smem + plan.w1);
+  const uint32_t w_u32 = pk_smem_u32(smem + plan.w);
   const uint32_t x_u32 = pk_smem_u32(smem + plan.x);
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < PKD_X_STAGES_MAX; ++i) {
-      pk_mbar_init(x_full + i, 1);  // the producer's arrive.expect_tx with the byte count of the stage's copies
-      pk_mbar_init(x_empty + i, PKD_TW);
+      pk_mbar_init(x_full + i, PKD_XPW);  // each X producer warp's arrive.expect_tx with the byte count of its copies
+      pk_mbar_init(x_empty + i, PKD_TW / 2);  // the eight warps of the tile's set
     }
     for (int i = 0; i < PKD_A_STAGES; ++i) {
-      pk_mbar_init(a_full + i, PKD_TW);
+      pk_mbar_init(a_full + i, PKD_TW / 2);
       pk_mbar_init(a_empty + i, 1);
     }
     for (int i = 0; i < PKD_W_STAGES; ++i) {
@@ -219,15 +234,13 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
   if (warp == PKD_PRODUCER) {
     // ---- TMA producer: biases / head / hidden operands once, then the W0 k-blocks in consumption order ----
     if (lane == 0) {
-      pk_mbar_expect_tx(wbar, (uint32_t)(lay.n_layers * HP + HP + 4) * 4u + (uint32_t)n_hidden * PKT_SET_BYTES);
+      pk_mbar_expect_tx(wbar, (uint32_t)(lay.n_layers * HP + HP + 4) * 4u);
       for (int l = 0; l < lay.n_layers; ++l) pk_bulk_load(s_small + HP * l, prep + lay.b[l], HP * 4u, wbar);
       pk_bulk_load(s_small + HP * lay.n_layers, prep + lay.wout, HP * 4u, wbar);
       pk_bulk_load(s_small + HP * lay.n_layers + HP, prep + lay.bout, 16u, wbar);
-      for (int l = 1; l <= n_hidden; ++l)
-        pk_bulk_load(smem + plan.w1 + (unsigned)(l - 1) * PKT_SET_BYTES, prep + lay.tc[l], PKT_SET_BYTES, wbar);
       uint32_t wit = 0;
       unsigned long long* ptr = blockIdx.x == 0 ? trace : nullptr;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
         for (int kb = 0; kb < NKB; ++kb, ++wit) {
           const int ws = (int)(wit % PKD_W_STAGES);
           const uint32_t wph = (wit / PKD_W_STAGES) & 1u;
@@ -238,26 +251,38 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
           pk_bulk_load(smem + plan.w + (unsigned)ws * PKD_W_STAGE, prep + lay.tc0 + (size_t)kb * (PKD_W_STAGE >> 2),
                        PKD_W_STAGE, w_full + ws);
         }
+        // the hidden matrices ride the same ring during the epilogue (one stage each; a single hidden layer's matrix
+        // is loaded once for the pair's two tiles)
+        for (int tl = 0; tl < 2 * n_hidden; ++tl) {
+          if (n_hidden == 1 && tl == 1) break;
+          const int ws = (int)(wit % PKD_W_STAGES);
+          pk_mbar_wait(w_empty + ws, ((wit / PKD_W_STAGES) & 1u) ^ 1u);
+          pk_mbar_expect_tx(w_full + ws, PKT_SET_BYTES);
+          pk_bulk_load(smem + plan.w + (unsigned)ws * PKD_W_STAGE, prep + lay.tc[1 + tl % n_hidden], PKT_SET_BYTES, w_full + ws);
+          ++wit;
+        }
       }
     }
     __syncwarp();
-  } else if (warp == PKD_XPRODUCER) {
-    // ---- TMA producer of the X stream: lane i < nb copies the 16-byte-aligned cover of battle i's k-block ----
+  } else if (warp >= PKD_XPRODUCER && warp < PKD_XPRODUCER + PKD_XPW) {
+    // ---- TMA producers of the X stream: a lane copies the 16-byte-aligned cover of one battle's k-block ----
+    const int pb = PKD_XPW * lane + (warp - PKD_XPRODUCER);  // this lane's battle within a tile
     const unsigned long long feat_addr = (unsigned long long)feat;
     const unsigned long long arr_end16 = (feat_addr + (unsigned long long)B * L * 4ull) & ~15ull;
     uint32_t xit = 0;
-    unsigned long long* ptr = (blockIdx.x == 0 && lane == 0) ? trace : nullptr;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const long long b = (long long)tile * nb + lane;
-      const bool mine = lane < nb && b < B;
-      for (int kb = 0; kb < NKB; ++kb, ++xit) {
+    unsigned long long* ptr = (blockIdx.x == 0 && lane == 0 && warp == PKD_XPRODUCER) ? trace : nullptr;
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+      for (int kt = 0; kt < 2 * NKB; ++kt, ++xit) {
+        const int kb = kt >> 1, tile = 2 * pair + (kt & 1);
+        const long long b = (long long)tile * nb + pb;
+        const bool mine = pb < nb && tile < ntiles && b < B;
         const int xs = (int)(xit % (uint32_t)XS);
         pkd_trace(ptr, 2, xit, 2);
         pk_mbar_wait(x_empty + xs, ((xit / (uint32_t)XS) & 1u) ^ 1u);
         pkd_trace(ptr, 2, xit, 3);
         uint32_t bytes = 0;
         unsigned long long src = 0;
-        unsigned char* dst = smem + plan.x + (unsigned)xs * plan.x_stage + (unsigned)lane * plan.piece;
+        unsigned char* dst = smem + plan.x + (unsigned)xs * plan.x_stage + (unsigned)pb * plan.piece;
         if (mine) {
           const unsigned long long addr =
               feat_addr + 4ull * ((unsigned long long)b * L + (unsigned long long)kb * PKD_KBF * A);
@@ -285,45 +310,53 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
     }
   } else if (warp == PKD_MMA) {
     // ---- MMA issuer ----
+    // Measured: a tcgen05.mma whose A operand is in tensor memory issues every ~131 cycles whatever its N (64 or 128),
+    // whether successive MMAs share an accumulator or alternate between two, and two issuing warps are slower (~200).
     if (lane == 0) {
       constexpr uint32_t idesc_hi = pkt_instr_desc(128, 128), idesc_lo = pkt_instr_desc(128, 64);
       uint32_t ait = 0, wit = 0, hfpar = 0;
       unsigned long long* mtr = blockIdx.x == 0 ? trace : nullptr;
       pk_mbar_wait(wbar, 0);
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        for (int kb = 0; kb < NKB; ++kb, ++ait, ++wit) {
-          const int as = (int)(ait % PKD_A_STAGES);
-          const uint32_t aph = (ait / PKD_A_STAGES) & 1u;
+      for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+        for (int kt = 0; kt < 2 * NKB; ++kt, ++ait) {
+          const int kb = kt >> 1, as = kt & 1;  // the tile of the pair = its A stage = its accumulator
+          const uint32_t aph = (ait >> 1) & 1u;
           const int ws = (int)(wit % PKD_W_STAGES);
-          const uint32_t wph = (wit / PKD_W_STAGES) & 1u;
           pkd_trace(mtr, 1, ait, 0);
           pk_mbar_wait(a_full + as, aph);
           pkd_trace(mtr, 1, ait, 1);
-          pk_mbar_wait(w_full + ws, wph);
+          if (as == 0) pk_mbar_wait(w_full + ws, (wit / PKD_W_STAGES) & 1u);
           pkd_trace(mtr, 1, ait, 2);
           pkw_tc_fence_after();
           const uint32_t fl = lo_flag[as * 2 + (int)aph];
           lo_flag[as * 2 + (int)aph] = 0u;  // set again two uses of this stage later, after the commit below
           const uint32_t ta = tmem_base + PKD_COL_A + 128u * (uint32_t)as, tw = w_u32 + (uint32_t)ws * PKD_W_STAGE;
+          const uint32_t tacc = tmem_base + PKD_COL_ACC0 + 128u * (uint32_t)as;
 #pragma unroll
-          for (int s = 0; s < PKD_KBF / 8; ++s) {  // UMMA_K = 8 fp32: 16 TMEM columns (hi | lo) of A, 32 B of the swizzle atom of W
+          for (int s = 0; s < PKD_KBF / 8; ++s) {  // UMMA_K = 8 fp32: 8 TMEM columns of A (hi; lo 64 further), 32 B of the swizzle atom of W
             const uint64_t bd = pkw_smem_desc_k128(tw + (uint32_t)(s >> 2) * PKD_W_TILE) + 2u * (uint64_t)(s & 3);
-            pkd_mma_ts(tmem_base + PKD_COL_ACC0, ta + 16u * (uint32_t)s, bd, idesc_hi, (kb | s) != 0 ? 1u : 0u);
-            if (fl) pkd_mma_ts(tmem_base + PKD_COL_ACC0, ta + 16u * (uint32_t)s + 8u, bd, idesc_lo, 1u);
+            pkd_mma_ts(tacc, ta + 8u * (uint32_t)s, bd, idesc_hi, (kb | s) != 0 ? 1u : 0u);
+            if (fl) pkd_mma_ts(tacc, ta + 64u + 8u * (uint32_t)s, bd, idesc_lo, 1u);
           }
           pkd_trace(mtr, 1, ait, 3);
-          pkw_mma_commit(w_empty + ws);
+          if (as == 1) {
+            pkw_mma_commit(w_empty + ws);
+            ++wit;
+          }
           pkw_mma_commit(a_empty + as);
           pkd_trace(mtr, 1, ait, 4);
         }
         pkw_mma_commit(acc0_full);
-        for (int l = 1; l <= n_hidden; ++l) {
+        for (int tl = 0; tl < 2 * n_hidden; ++tl) {  // the pair's two tiles in turn
+          const int l = 1 + tl % n_hidden;
           pk_mbar_wait(hid_full, hfpar);
           hfpar ^= 1u;
           pkw_tc_fence_after();
           // D (128 x 64) = H (128 x 64, TMEM) . W_l^T:  lo*hi + hi*lo + hi*hi
           constexpr uint32_t idesc_h = pkt_instr_desc(128, 64);
-          const uint32_t tb = w1_u32 + (uint32_t)(l - 1) * PKT_SET_BYTES;
+          const int ws = (int)(wit % PKD_W_STAGES);
+          if (n_hidden > 1 || tl == 0) pk_mbar_wait(w_full + ws, (wit / PKD_W_STAGES) & 1u);
+          const uint32_t tb = w_u32 + (uint32_t)ws * PKD_W_STAGE;
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
             const uint32_t th = tmem_base + PKD_COL_HA + 16u * (uint32_t)s;
@@ -335,13 +368,21 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
             pkd_mma_ts(tmem_base + PKD_COL_HACC, th, bhi, idesc_h, 1u);
           }
           pkw_mma_commit(hidacc_full);
+          if (n_hidden > 1 || tl == 1) {
+            pkw_mma_commit(w_empty + ws);
+            ++wit;
+          }
         }
       }
     }
     __syncwarp();
   } else {
     // ---- loading / splitting / epilogue warps ----
-    const int wq = warp & 3, cg = warp >> 2;  // TMEM lane quarter this warp may access; its k / channel group
+    // Main loop: warps 0-7 feed tile 0 of the pair, warps 8-15 tile 1 (each its own A stage and every other X stage), so
+    // the two sets drift apart and one set's shared-memory reads overlap the other's tensor-memory stores.  Within a set
+    // warp (q, half) owns TMEM lane quarter q and the k-block's rows 32 half .. 32 half + 31.
+    const int tset = warp >> 3, wq = warp & 3, khalf = (warp >> 2) & 1;
+    const int cg = warp >> 2;                 // epilogue: this warp's 16-channel group (all sixteen warps, one tile at a time)
     const int row = 32 * wq + lane;           // this thread's accumulator row = TMEM lane
     const bool row_ok = row < rows;
     const int rbi = row / A;                  // its battle within the tile, its action column
@@ -349,66 +390,69 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
     const unsigned long long feat_addr = (unsigned long long)feat;
     const uint32_t tlane = tmem_base + ((uint32_t)(32 * wq) << 16);
     // element (k, ra) of this row's battle inside a stage: piece rbi, float index k * A + ra (+ the piece's misalignment)
-    const uint32_t src_row = (uint32_t)rbi * plan.piece + (uint32_t)ra * 4u + (uint32_t)((PKD_KBF / 4) * cg * A) * 4u;
+    const uint32_t src_row = (uint32_t)rbi * plan.piece + (uint32_t)ra * 4u + (uint32_t)((PKD_KBF / 2) * khalf * A) * 4u;
     uint32_t tpar = 0, hpar = 0;
     bool first = true;
     unsigned long long* ttr = (blockIdx.x == 0 && threadIdx.x == 0) ? trace : nullptr;
-    const uint32_t my_tiles = (uint32_t)((ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x);
-    const uint32_t n_it = my_tiles * (uint32_t)NKB;
-    // the loads of iteration j: this thread's sixteen X values of k-block j -> registers; then the stage is released
-    int ltile = blockIdx.x, lkb = 0;
-    uint32_t lit = 0;
-    float xn[PKD_KBF / 4];
-    auto load_x = [&]() {
-      const int xs = (int)(lit % (uint32_t)XS);
-      pk_mbar_wait(x_full + xs, (lit / (uint32_t)XS) & 1u);
-      const uint32_t mis =
-          (uint32_t)((feat_addr + 4ull * (unsigned long long)((long long)ltile * nb + rbi) * (unsigned long long)L) & 15ull);
-      const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_row + mis;
-      const int k0 = lkb * PKD_KBF + (PKD_KBF / 4) * cg;
+    uint32_t sit = 0;  // this set's iteration count: (pair, k-block)
+    bool lo_clean[2] = {false, false};  // this warp's two lo groups of its A stage hold zeros
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+      const int tile0 = 2 * pair;
+      const uint32_t mis = (uint32_t)(
+          (feat_addr + 4ull * (unsigned long long)((long long)(tile0 + tset) * nb + rbi) * (unsigned long long)L) & 15ull);
+      for (int kb = 0; kb < NKB; ++kb, ++sit) {
+        const uint32_t xit = 2u * sit + (uint32_t)tset;  // X stages alternate between the pair's tiles
+        const int xs = (int)(xit % (uint32_t)XS);
+        const uint32_t aph = sit & 1u;
+        pkd_trace(ttr, 0, sit, 0);
+        pk_mbar_wait(x_full + xs, (xit / (uint32_t)XS) & 1u);
+        pkd_trace(ttr, 0, sit, 1);
+        const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_row + mis;
+        const int k0 = kb * PKD_KBF + (PKD_KBF / 2) * khalf;
+        float x[PKD_KBF / 2];
 #pragma unroll
-      for (int j = 0; j < PKD_KBF / 4; ++j) xn[j] = (row_ok && k0 + j < lay.C) ? pkd_lds(xb + (uint32_t)(j * A) * 4u) : 0.0f;
-      __syncwarp();
-      if (lane == 0) pkw_mbar_arrive(x_empty + xs);
-      ++lit;
-      if (++lkb == NKB) {
-        lkb = 0;
-        ltile += gridDim.x;
-      }
-    };
-    load_x();
-    int tile = blockIdx.x, kb = 0;
-    for (uint32_t it = 0; it < n_it; ++it) {
-      const int as = (int)(it % PKD_A_STAGES);
-      const uint32_t aph = (it / PKD_A_STAGES) & 1u;
-      float x[PKD_KBF / 4];
+        for (int j = 0; j < PKD_KBF / 2; ++j) x[j] = (row_ok && k0 + j < lay.C) ? pkd_lds(xb + (uint32_t)(j * A) * 4u) : 0.0f;
+        pkd_trace(ttr, 0, sit, 2);
+        __syncwarp();
+        if (lane == 0) pkw_mbar_arrive(x_empty + xs);
+        pk_mbar_wait(a_empty + tset, aph ^ 1u);
+        pkw_tc_fence_after();
+        pkd_trace(ttr, 0, sit, 3);
+        static_assert(PKD_KBF == 64, "thirty-two values per thread: four K-steps");
+        // A stage: columns 0-63 the hi parts (column = k), 64-127 the lo parts.  One-hot rows have no lo part: a warp
+        // whose sixteen-column group of lo is zero and already holds zeros ("clean") does not store it again, which
+        // halves the tensor-memory stores of all but the first k-block.
+        bool any_lo = false;
 #pragma unroll
-      for (int j = 0; j < PKD_KBF / 4; ++j) x[j] = xn[j];
-      pkd_trace(ttr, 0, it, 0);
-      if (it + 1u < n_it) load_x();  // the next k-block's values, in flight under the split and the TMEM store below
-      pkd_trace(ttr, 0, it, 3);
-      pk_mbar_wait(a_empty + as, aph ^ 1u);
-      pkw_tc_fence_after();
-      pkd_trace(ttr, 0, it, 4);
-      {
-        static_assert(PKD_KBF == 64, "sixteen values per thread: two K-steps");
-        const uint32_t lo_or = pkd_split_store16(tlane + PKD_COL_A + 128u * (uint32_t)as + 32u * (uint32_t)cg, x);
-        const bool any_lo = __any_sync(0xffffffffu, (lo_or << 1) != 0u);
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t vh[16], vl[16];
+          uint32_t lo_or = 0u;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float hi = pk_tf32_hi(x[16 * hh + j]), lo = x[16 * hh + j] - hi;
+            vh[j] = __float_as_uint(hi);
+            vl[j] = __float_as_uint(lo);
+            lo_or |= __float_as_uint(lo);
+          }
+          const uint32_t tcol = tlane + PKD_COL_A + 128u * (uint32_t)tset + 32u * (uint32_t)khalf + 16u * (uint32_t)hh;
+          pkd_tmem_st16(tcol, vh);
+          const bool nz = __any_sync(0xffffffffu, (lo_or << 1) != 0u);
+          if (nz || !lo_clean[hh]) pkd_tmem_st16(tcol + 64u, vl);  // values, or the zeros that make the group clean
+          lo_clean[hh] = !nz;
+          any_lo |= nz;
+        }
         pkd_tmem_st_wait();
         pkw_tc_fence_before();
         __syncwarp();
+        pkd_trace(ttr, 0, sit, 4);
         if (lane == 0) {
-          if (any_lo) lo_flag[as * 2 + (int)aph] = 1u;
-          pkw_mbar_arrive(a_full + as);
+          if (any_lo) lo_flag[tset * 2 + (int)aph] = 1u;
+          pkw_mbar_arrive(a_full + tset);
         }
+        pkd_trace(ttr, 0, sit, 5);
       }
-      pkd_trace(ttr, 0, it, 5);
-      if (++kb < NKB) continue;
-      kb = 0;
-      const long long b0 = (long long)tile * nb;
-      tile += gridDim.x;
-      const uint32_t xit = it + 1u;
-      // ---- layer-0 epilogue: relu(D[:, j] + D[:, 64 + j] + b0[j]) -> the hidden layer's A operand (TMEM) ----
+      const uint32_t xit = sit;
+      // ---- epilogue of the pair: relu(D[:, j] + D[:, 64 + j] + b0[j]) -> the hidden layer's A operand (TMEM) ----
       pkd_trace(ttr, 0, xit - 1u, 6);
       pk_mbar_wait(acc0_full, tpar);
       tpar ^= 1u;
@@ -417,10 +461,12 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
         pk_mbar_wait(wbar, 0);
         first = false;
       }
+      for (int t = 0; t < 2; ++t) {
+      const long long b0 = (long long)(tile0 + t) * nb;
       {
         uint32_t v1[16], v2[16];
-        pkd_tmem_ld16(tlane + PKD_COL_ACC0 + 16u * (uint32_t)cg, v1);
-        pkd_tmem_ld16(tlane + PKD_COL_ACC0 + 64u + 16u * (uint32_t)cg, v2);
+        pkd_tmem_ld16(tlane + PKD_COL_ACC0 + 128u * (uint32_t)t + 16u * (uint32_t)cg, v1);
+        pkd_tmem_ld16(tlane + PKD_COL_ACC0 + 128u * (uint32_t)t + 64u + 16u * (uint32_t)cg, v2);
         pkw_tmem_ld_wait();
         float h[16];
 #pragma unroll
@@ -474,6 +520,8 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
                  s_small[HP * lay.n_layers + HP];
       }
       pkt_named_barrier(2, 32 * PKD_TW);  // s_part is rewritten by the next tile's head
+      }
+      if (tset == 0) lo_clean[0] = lo_clean[1] = false;  // the hidden layers' A operand was written over A stage 0
     }
   }
   pkw_tc_fence_before();

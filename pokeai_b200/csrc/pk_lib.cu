@@ -460,8 +460,8 @@ extern "C" int pk_mlp_forward(const float* prepared, int n_layers, int n_channel
     if (plan.x_stages >= 2) {
       int rc = pk_set_smem(pk_dense_tc_kernel, plan.total);
       if (rc) return rc;
-      const int nb = pkd_battles_per_tile(A), ntiles = (B + nb - 1) / nb;
-      const int tgrid = ntiles < g.sm_count ? ntiles : g.sm_count;
+      const int nb = pkd_battles_per_tile(A), npairs = ((B + nb - 1) / nb + 1) / 2;  // a CTA works on pairs of tiles
+      const int tgrid = npairs < g.sm_count ? npairs : g.sm_count;
       pk_dense_tc_kernel<<<tgrid, PKD_WARPS * 32, plan.total, st>>>(feat, B, A, prepared, lay, q, (unsigned)g.max_smem,
                                                                     g.trace);
       PK_CUDA(cudaGetLastError());

@@ -21,4 +21,9 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:pk_d
     python tools/prof_decide.py > $OUT/ncu_full_r02.log 2>&1
 echo "ncu full rc=$?"
 ncu -i $OUT/prof_r02.ncu-rep --page raw --csv > $OUT/r02_ncu_full_raw.csv 2>/dev/null
+echo "== dense forward: timeline of the roles, ncu full capture"
+B=65536 IT0=20 IT1=44 timeout 300 python tools/trace_dense.py > $OUT/r02_trace_dense.txt 2>&1; tail -2 $OUT/r02_trace_dense.txt
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:pk_dense_tc_kernel -s 2 -c 1 -f -o $OUT/prof_dense_r02 \
+    python tools/prof_dense.py > $OUT/ncu_dense_r02.log 2>&1
+echo "ncu dense rc=$?"
 ls -la $OUT | head -40

@@ -11,7 +11,7 @@ LIB = Path(__file__).resolve().parents[1] / "pokeai_b200" / "_lib" / "libpokeai_
 INTEREST = ["FFMA2", "FFMA", "FADD", "LDS", "STS", "LDG", "STG", "UBLKCP", "UTMALDG", "UTMASTG", "UTCHMMA", "UTCQMMA",
             "LDTM", "STTM", "UTCBAR", "SYNCS", "LDGSTS", "HMMA", "SHFL", "BAR", "RED", "ATOM", "MUFU", "ACQBULK"]
 KEEP = re.compile(r"pk_decide_kernelILi2ELi9ELi512ELb0|pk_decide2_kernelILi4ELi9ELb[01]|pk_decide_tc_kernelILi9|"
-                  r"pk_dense_forward_kernelILi2ELi9|pk_dqn_backward_kernelILi2ELi2ELb1|pk_wide_gemm_kernel|"
+                  r"pk_dense_forward_kernelILi2ELi9|pk_dense_tc_kernel|pk_dqn_backward_kernelILi2ELi2ELb1|pk_wide_gemm_kernel|"
                   r"pk_wide_encode|pk_peer_clamp_adam|pk_clamp_adam_kernel|pk_dqn_reduce_flat|pk_select_kernel|pk_wide_head")
 
 

@@ -71,6 +71,29 @@ if rep.exists():
                            capture_output=True, text=True).stdout
         (P / f"{rnd}_ncu_lines_{name}.txt").write_text(o)
 
+# 3. dense-input forward: full capture of pk_dense_tc_kernel at 65 536 states
+rep = G / f"prof_dense_{tag}.ncu-rep"
+if rep.exists():
+    out = subprocess.run(["ncu", "-i", str(rep), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    keep = re.compile(r"^(Kernel Name|Grid Size|Block Size|gpu__time_duration.sum|dram__bytes_(read|write).sum$|"
+                      r"gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed|launch__registers_per_thread$|"
+                      r"sm__warps_active.avg.pct_of_peak_sustained_active|smsp__issue_active.avg.pct_of_peak_sustained_active|"
+                      r"smsp__inst_executed.sum$|lts__t_sector_hit_rate.pct|lts__t_bytes.sum$|sm__cycles_elapsed.avg$|"
+                      r"sm__pipe_tensor_subpipe.*cycles_active.avg.pct_of_peak_sustained_active|sm__inst_executed_pipe_tensor.*sum$|"
+                      r"l1tex__data_pipe_lsu_wavefronts_mem_shared.sum$|l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum$|"
+                      r"smsp__average_warps_issue_stalled_(long_scoreboard|short_scoreboard|wait|barrier|mio_throttle|lg_throttle|membar|sleeping)_per_issue_active.ratio)")
+    with open(P / f"{rnd}_ncu_dense_summary.txt", "w") as f:
+        f.write("# ncu --set full --clock-control none --import-source on -k regex:pk_dense_tc_kernel  python tools/prof_dense.py\n")
+        f.write("# pk_mlp_forward on dense (65536, 617, 9) fp32 features, default MLP 2x64 (one isolated launch, cold L2)\n")
+        for i, h in enumerate(hdr):
+            if keep.search(h):
+                f.write(f"{h:100s} {units[i]:16s} " + "  ".join(f"{r[i][:40]:>16s}" for r in data) + "\n")
+    print(open(P / f"{rnd}_ncu_dense_summary.txt").read()[:3000])
+if (G / f"{rnd}_trace_dense.txt").exists():
+    shutil.copy(G / f"{rnd}_trace_dense.txt", P / f"{rnd}_trace_dense.txt")
+
 for name in (f"bench_{tag}.json", f"bench_ref_{tag}.json", f"quick_{tag}.log", f"pytest_{tag}.log", f"smoke_{tag}.log", f"gpu_{tag}.txt"):
     if (G / name).exists():
         shutil.copy(G / name, P / name.replace(f"_{tag}", f"_{rnd}"))

@@ -31,7 +31,7 @@ torch.cuda.synchronize()
 N.check(N.lib().pk_debug_set_trace(None))
 t = tr.cpu().numpy()
 t0 = t[t > 0].min()
-roles = {0: ["top", "-", "-", "next lds", "a_empty", "tmem st", "(tile end) loop out", "(tile end) head done"],
+roles = {0: ["top", "x_full", "lds issued", "a_empty", "tmem st", "arrived", "(tile end) loop out", "(tile end) head done"],
          1: ["top", "a_full", "w_full", "issued", "committed"],
          2: ["W top", "w_empty", "X top", "x_empty", "x issued"]}
 lo, hi = int(os.environ.get("IT0", 20)), int(os.environ.get("IT1", 44))
