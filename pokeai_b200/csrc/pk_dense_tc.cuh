@@ -33,7 +33,7 @@
 // Tensor memory (512 columns): two layer-0 accumulators of 128, A stages 2 x 128 (the hidden layers' A operand and
 // accumulator alias them during the epilogue).
 //
-// Measured on B200, 65 536 states: 375 - 395 us = 0.57 - 0.60 of the HBM roofline (FP32-pipe kernel:
+// Measured on B200, 65 536 states: 380 - 396 us = 0.56 - 0.59 of the HBM roofline (FP32-pipe kernel:
 // 569 us, 0.39); 4 096 states 31 - 33 us (54).  What was learned on the way, each from a timeline of the roles
 // (tools/trace_dense.py) or a microbenchmark (tools/micro/bulk_load_bw.cu):
 //   * A tiles in SHARED memory (transposed by LDS + STS): 136 KB of shared-memory traffic per 16 KB of input -- the
@@ -72,7 +72,7 @@
                                     // X_hi W_hi + X_lo W_hi | X_hi W_lo
 #define PKD_COL_A 256u              // A stages (one per tile of the pair), 128 columns each: hi parts (64, column = k), lo parts (64)
 #define PKD_COL_HA PKD_COL_A        // hidden A operand (per K-step of 8: hi (8), lo (8)): aliases A stage 0, idle during the epilogue
-#define PKD_COL_HACC (PKD_COL_A + 128u)  // hidden-layer accumulator (64 columns): aliases the hi half of A stage 1
+#define PKD_COL_HACC (PKD_COL_A + 128u)  // hidden-layer accumulator (H_hi W_hi + H_lo W_hi | H_hi W_lo): aliases A stage 1
 
 struct PkdSmemPlan {
   unsigned w;         // W stages: W0 k-blocks, and the hidden matrices (PkLayout::tc, one stage each) during the epilogue
@@ -258,7 +258,14 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
           const int ws = (int)(wit % PKD_W_STAGES);
           pk_mbar_wait(w_empty + ws, ((wit / PKD_W_STAGES) & 1u) ^ 1u);
           pk_mbar_expect_tx(w_full + ws, PKT_SET_BYTES);
-          pk_bulk_load(smem + plan.w + (unsigned)ws * PKD_W_STAGE, prep + lay.tc[1 + tl % n_hidden], PKT_SET_BYTES, w_full + ws);
+          // PkLayout::tc holds [hi kb0][hi kb1][lo kb0][lo kb1]; the stage gets [hi kb0][lo kb0][hi kb1][lo kb1], so that
+          // each k-block is one 128-row operand [W_hi ; W_lo] as for layer 0
+          const float* src = prep + lay.tc[1 + tl % n_hidden];
+          unsigned char* dst = smem + plan.w + (unsigned)ws * PKD_W_STAGE;
+          for (int kbh = 0; kbh < 2; ++kbh)
+            for (int part = 0; part < 2; ++part)
+              pk_bulk_load(dst + (unsigned)(2 * kbh + part) * PKT_KB_BYTES,
+                           src + (size_t)part * PK_TC_TILE_FLOATS + (size_t)kbh * (PKT_KB_BYTES >> 2), PKT_KB_BYTES, w_full + ws);
           ++wit;
         }
       }
@@ -352,20 +359,17 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
           pk_mbar_wait(hid_full, hfpar);
           hfpar ^= 1u;
           pkw_tc_fence_after();
-          // D (128 x 64) = H (128 x 64, TMEM) . W_l^T:  lo*hi + hi*lo + hi*hi
-          constexpr uint32_t idesc_h = pkt_instr_desc(128, 64);
+          // D (128 x 128) = H_hi . [W_hi ; W_lo]^T, D[:, 0:64] += H_lo . W_hi^T  (H in TMEM)
+          constexpr uint32_t idesc_h2 = pkt_instr_desc(128, 128), idesc_h = pkt_instr_desc(128, 64);
           const int ws = (int)(wit % PKD_W_STAGES);
           if (n_hidden > 1 || tl == 0) pk_mbar_wait(w_full + ws, (wit / PKD_W_STAGES) & 1u);
           const uint32_t tb = w_u32 + (uint32_t)ws * PKD_W_STAGE;
 #pragma unroll
           for (int s = 0; s < 8; ++s) {
             const uint32_t th = tmem_base + PKD_COL_HA + 16u * (uint32_t)s;
-            const uint64_t bhi = pkw_smem_desc_k128(tb + (uint32_t)(s >> 2) * PKT_KB_BYTES) + 2u * (uint64_t)(s & 3);
-            const uint64_t blo =
-                pkw_smem_desc_k128(tb + PKT_TILE_BYTES + (uint32_t)(s >> 2) * PKT_KB_BYTES) + 2u * (uint64_t)(s & 3);
-            pkd_mma_ts(tmem_base + PKD_COL_HACC, th + 8u, bhi, idesc_h, s != 0 ? 1u : 0u);
-            pkd_mma_ts(tmem_base + PKD_COL_HACC, th, blo, idesc_h, 1u);
-            pkd_mma_ts(tmem_base + PKD_COL_HACC, th, bhi, idesc_h, 1u);
+            const uint64_t bd = pkw_smem_desc_k128(tb + (uint32_t)(s >> 2) * PKD_W_TILE) + 2u * (uint64_t)(s & 3);
+            pkd_mma_ts(tmem_base + PKD_COL_HACC, th, bd, idesc_h2, s != 0 ? 1u : 0u);
+            pkd_mma_ts(tmem_base + PKD_COL_HACC, th + 8u, bd, idesc_h, 1u);
           }
           pkw_mma_commit(hidacc_full);
           if (n_hidden > 1 || tl == 1) {
@@ -483,8 +487,14 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
         hpar ^= 1u;
         pkw_tc_fence_after();
         uint32_t v[16];
-        pkd_tmem_ld16(tlane + PKD_COL_HACC + 16u * (uint32_t)cg, v);
-        pkw_tmem_ld_wait();
+        {
+          uint32_t v2[16];
+          pkd_tmem_ld16(tlane + PKD_COL_HACC + 16u * (uint32_t)cg, v);
+          pkd_tmem_ld16(tlane + PKD_COL_HACC + 64u + 16u * (uint32_t)cg, v2);
+          pkw_tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+        }
         const float* bl = s_small + HP * l + 16 * cg;
         if (l < n_hidden) {
           float h[16];
@@ -521,7 +531,7 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
       }
       pkt_named_barrier(2, 32 * PKD_TW);  // s_part is rewritten by the next tile's head
       }
-      if (tset == 0) lo_clean[0] = lo_clean[1] = false;  // the hidden layers' A operand was written over A stage 0
+      lo_clean[0] = lo_clean[1] = false;  // the hidden layers' A operand and accumulator were written over the A stages
     }
   }
   pkw_tc_fence_before();

@@ -2,4 +2,3 @@
 set -u
 echo "== pytest dense tc"; timeout 300 python -m pytest tests/test_gpu_decide.py -m gpu -x -q -k "dense" 2>&1 | tail -5
 for B in 4096 65536; do B=$B timeout 120 python tools/quick_time.py 2>&1 | grep "^dense"; done
-B=65536 IT0=10 IT1=22 timeout 120 python tools/trace_dense.py 2>&1 | grep -A14 "^role [012]" | grep -v "^--"
