@@ -133,6 +133,11 @@ struct PkwGemmArgs {
   int relu;
   int tma_store;          // out_bf (and only out_bf) is written by TMA stores through map_o
   int ksplit;             // >= 1: the contraction is cut into ksplit ranges; range s writes out_f32 + s * M * N
+  // fused 1-channel head (mlp_model.py:26-28): head_part[m][2 nb + half] = sum over the half tile's 128 columns of
+  // bf16(act(acc + bias))[n] * head_w[n]; pk_wide_head_sum_kernel adds the 2 N / 256 partials of a row in a fixed order.
+  // With out_bf == nullptr the activations themselves are never written (inference: 151 MB at 4 096 states x 2048).
+  const float* head_w;    // (N,) fp32 or null
+  float* head_part;       // (M, 2 * ceil(N / 256)) fp32
 };
 
 // MN == 0:  Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
@@ -269,6 +274,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       pkw_tc_fence_after();
       const int row = mb * PKW_BM + quarter * 32 + lane;
       const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * PKW_BN);
+      float hs0 = 0.0f, hs1 = 0.0f, hs2 = 0.0f, hs3 = 0.0f;  // fused head: this row's partial over the warp's columns
 #pragma unroll 1
       for (int ch = ch0; ch < ch0 + CHW; ++ch) {
         uint32_t v[32];
@@ -305,6 +311,16 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               if (!(mf.x > 0.0f)) f[j + 2 * t] = 0.0f;
               if (!(mf.y > 0.0f)) f[j + 2 * t + 1] = 0.0f;
             }
+          }
+        }
+        if (g.head_w != nullptr) {  // the head reads the activations as the next layer would: rounded to bf16
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 wv = __ldg(reinterpret_cast<const float4*>(g.head_w + n0 + j));
+            hs0 = fmaf(__bfloat162float(__float2bfloat16_rn(f[j])), wv.x, hs0);
+            hs1 = fmaf(__bfloat162float(__float2bfloat16_rn(f[j + 1])), wv.y, hs1);
+            hs2 = fmaf(__bfloat162float(__float2bfloat16_rn(f[j + 2])), wv.z, hs2);
+            hs3 = fmaf(__bfloat162float(__float2bfloat16_rn(f[j + 3])), wv.w, hs3);
           }
         }
         if (g.tma_store) {
@@ -355,6 +371,8 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           }
         }
       }
+      if (g.head_w != nullptr && row < g.M)
+        g.head_part[(size_t)row * (2 * n_nblk) + 2 * nb + ((warp - 2) >> 2)] = (hs0 + hs1) + (hs2 + hs3);
       pkw_tc_fence_before();
       __syncwarp();
       if (lane == 0) pkw_mbar_arrive(tempty + as);
@@ -458,6 +476,18 @@ pk_wide_head_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) q[m] = s + __ldg(bout);
+}
+
+// the fused head's partials (PkwGemmArgs::head_part) -> q[m] = sum of the row's nparts partials, in order, + b_out
+__global__ void __launch_bounds__(256)
+pk_wide_head_sum_kernel(const float* __restrict__ part, int nparts, const float* __restrict__ bout, int M,
+                        float* __restrict__ q) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= M) return;
+  const float* p = part + (size_t)m * nparts;
+  float s = 0.0f;
+  for (int i = 0; i < nparts; ++i) s += p[i];
+  q[m] = s + __ldg(bout);
 }
 
 // fp32 (rows, cols) row-major -> bf16 (rows, cols_pad), zero padded columns

@@ -1,8 +1,8 @@
 #!/bin/bash
 set -u
-for E in 0 1; do echo "== PK_EARLY_FILL=$E"; PK_EARLY_FILL=$E timeout 300 python -m pytest tests/test_gpu_decide.py -m gpu -x -q 2>&1 | tail -1
-for B in 4096 65536; do PK_EARLY_FILL=$E PK_PDL=1 B=$B timeout 120 python tools/quick_time.py 2>&1 | grep "^decide+feat"; done
-PK_EARLY_FILL=$E timeout 300 python bench.py --steps 20 --warmup 5 --cpu-seconds 0 --no-secondary --no-e2e | python -c "
+echo "== pytest wide"; timeout 600 python -m pytest tests/test_gpu_wide.py tests/test_gpu_agents.py -m gpu -x -q 2>&1 | tail -3
+for F in 1 0; do echo "== PK_WIDE_FUSED_HEAD=$F"; PK_WIDE_FUSED_HEAD=$F timeout 600 python bench.py --steps 5 --warmup 3 --cpu-seconds 0 --no-e2e --skip-legs shard65536,dense,update,wide_update,gpu_reference,concurrent64 | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('bench', d['value'], d['ms_per_step']/16*1e3, 'us/launch frac', d['roofline']['frac'])"
+d=json.loads(sys.stdin.read().strip().splitlines()[-1])
+for r in d['roofline']['secondary']: print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','per_s','decisions_per_s','ms_per_step','frac_burst','frac_sustained','error','tflops')})"
 done
