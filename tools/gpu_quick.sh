@@ -1,8 +1,13 @@
 #!/bin/bash
 set -u
-echo "== pytest wide"; timeout 600 python -m pytest tests/test_gpu_wide.py tests/test_gpu_agents.py -m gpu -x -q 2>&1 | tail -3
-for F in 1 0; do echo "== PK_WIDE_FUSED_HEAD=$F"; PK_WIDE_FUSED_HEAD=$F timeout 600 python bench.py --steps 5 --warmup 3 --cpu-seconds 0 --no-e2e --skip-legs shard65536,dense,update,wide_update,gpu_reference,concurrent64 | python -c "
+OUT=gpurun_out
+mkdir -p $OUT
+echo "== pytest update"; timeout 900 python -m pytest tests/test_gpu_update.py tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -3
+for NB in 32768 4096; do echo "== bench_update --batch $NB"; timeout 300 python bench_update.py --cpu-seconds 0 --steps 100 --batch $NB | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1])
-for r in d['roofline']['secondary']: print({k:(round(v,4) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','per_s','decisions_per_s','ms_per_step','frac_burst','frac_sustained','error','tflops')})"
-done
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['value'], d['ms_per_step'])"; done
+echo "== launches"; timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/r02_launches_update.csv python bench_update.py --cpu-seconds 0 --steps 3 --warmup 3 > /dev/null 2>&1; python - <<'PY'
+import csv
+rows=[r for r in csv.reader(open('gpurun_out/r02_launches_update.csv')) if len(r)>10 and r[0].isdigit()]
+for r in rows[-8:]: print(r[4][:60], r[-1])
+PY
