@@ -486,7 +486,7 @@ def b200_arm(args, rank, local_rank, world):
         if tf.exists():
             try:
                 tj = json.loads(tf.read_text())
-                traffic = tj.get(f"pk_decide_tc_kernel@B={B}", tj.get(f"pk_decide_kernel@B={B}"))
+                traffic = tj.get(f"pk_decide_kernel@B={B}")
             except Exception:
                 traffic = None
         line = {
@@ -495,8 +495,10 @@ def b200_arm(args, rank, local_rank, world):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, world),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "pk_decide_tc_kernel<9,14>" if (nl >= 2 and 32 < H <= 64) else
-                         "pk_decide_kernel",
+                         "traffic": traffic,
+                         "kernel": ("pk_decide_tc_kernel<9>" if (os.environ.get("PK_DECIDE_TC", "0") not in ("", "0")
+                                                                  and nl >= 2 and 32 < H <= 64)
+                                    else "pk_decide_kernel<2,9,512,0>"),
                          "algorithmic_bytes_per_launch": ALG_BYTES_PER_DECISION * B, "peak_source": peak_src,
                          "launch_us": launch_ms * 1e3, "launches_timed": n_launch,
                          "overlap": "programmatic dependent launch, opted into with pk_set_overlap_launches(1): the "
