@@ -532,7 +532,9 @@ def leg_concurrent64(ctx, n_battles=64, rounds=200):
            "us_per_decision": dt / max(1, n_dec) * 1e6, "rounds": rounds, "host_pack_us_per_round": t_pack * 1e6,
            "gpu_call_us_per_round": t_gpu * 1e6,
            "note": "latency-bound: 64 states fill 64 of 2 368 warp slots; the GPU call is launch + completion latency, "
-                   "the rest of the round is Python (request -> record, 13 us per request)"}
+                   "the rest of the round is the host side (request -> record: "
+                   + ("the C packer csrc/pkpack.c, ~5 us" if _c_packer_in_use() else "Python struct packer, ~13 us")
+                   + " per request, plus the policy callbacks in Python)"}
     # the reference serves the same 64 battles one at a time (sim.py:54-99): get_possible_actions, RLPolicyObservation,
     # FeatureExtractor.transform, MLPModel at batch 1, argmax -- timed here with its own classes when they are staged
     try:
@@ -566,6 +568,11 @@ def leg_concurrent64(ctx, n_battles=64, rounds=200):
     except Exception as e:  # a baseline figure never takes the leg down
         out["cpu_reference_error"] = f"{type(e).__name__}: {e}"[:200]
     return out
+
+
+def _c_packer_in_use():
+    from pokeai_b200 import protocol
+    return protocol._C_PACK is not None
 
 
 def run_all(ctx, skip=()):

@@ -17,6 +17,9 @@ CSRC = PKG / "csrc"
 LIB_DIR = PKG / "_lib"
 LIB_PATH = LIB_DIR / "libpokeai_b200.so"
 STAMP = LIB_DIR / "libpokeai_b200.stamp"
+PACK_SRC = CSRC / "pkpack.c"
+PACK_PATH = LIB_DIR / "_pkpack.so"          # CPython extension: the lock-step driver's request packer (host side only)
+PACK_STAMP = LIB_DIR / "_pkpack.stamp"
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
@@ -67,5 +70,28 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+def build_packer(force: bool = False):
+    """gcc-compile csrc/pkpack.c into _lib/_pkpack.so for THIS interpreter.  Returns the path, or None when the
+    Python headers or gcc are missing (protocol.pack_request_into then stays on its Python implementation)."""
+    import sysconfig
+    inc = sysconfig.get_paths().get("include")
+    gcc = shutil.which("gcc") or shutil.which("cc")
+    if not inc or not (Path(inc) / "Python.h").exists() or gcc is None:
+        return None
+    digest = hashlib.sha256(PACK_SRC.read_bytes() + sys.version.encode()).hexdigest()
+    if not force and PACK_PATH.exists() and PACK_STAMP.exists() and PACK_STAMP.read_text().strip() == digest:
+        return PACK_PATH
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    tmp = LIB_DIR / "_pkpack.so.tmp"
+    res = subprocess.run([gcc, "-O2", "-shared", "-fPIC", "-I", inc, "-o", str(tmp), str(PACK_SRC)],
+                         capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("gcc failed on pkpack.c:\n" + res.stdout + res.stderr)
+    os.replace(tmp, PACK_PATH)
+    PACK_STAMP.write_text(digest + "\n")
+    return PACK_PATH
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_packer(force="--force" in sys.argv))

@@ -69,6 +69,45 @@ def test_struct_packer_writes_the_same_bytes(cases, statuses, tables):
         pack_request_into(buf, 0, statuses[0], bad, tables)
 
 
+def test_c_packer_writes_the_same_bytes_and_raises_the_same(cases, statuses, tables):
+    """csrc/pkpack.c (the lock-step driver's packer when built) == pack_request_into_py: bytes, keys, exception types"""
+    from pokeai_b200 import build as b
+    from pokeai_b200 import protocol as P
+    from pokeai_b200.packed import PK_OBS_BYTES
+    if b.build_packer() is None:
+        pytest.skip("Python headers or gcc not available")
+    cpack = P._load_c_packer()
+    assert cpack is not None
+
+    def c_call(buf, off, bs, req, max_actions=9):
+        return cpack(buf, off, bs, req, tables.species_name_to_idx, tables.move_to_idx, tables.item_to_idx, max_actions,
+                     P.STATUS_CODE, P.STATUS_FNT, P.WEATHER_CODE)
+    for i, c in enumerate(cases):
+        bs = statuses[i % len(statuses)]
+        b1, b2 = bytearray(b"\xaa" * (3 * PK_OBS_BYTES)), bytearray(b"\xaa" * (3 * PK_OBS_BYTES))
+        k1 = P.pack_request_into_py(b1, PK_OBS_BYTES, bs, c["request"], tables)
+        k2 = c_call(b2, PK_OBS_BYTES, bs, c["request"])
+        assert k1 == k2 and b1 == b2, i
+    buf = bytearray(PK_OBS_BYTES)
+    big = [c for c in cases if len(c["possible_actions"]) > 3][0]["request"]
+    bad = copy.deepcopy(cases[0]["request"])
+    bad["side"]["pokemon"][0]["details"] = "Missingno, L50"
+    no_active = {k: v for k, v in cases[0]["request"].items() if k != "active"}
+    zero = copy.deepcopy(statuses[0])
+    zero.side_statuses[zero.side_friend].active.hp_max = 0
+    for exc, bs, req, kw in ((ValueError, statuses[0], big, {"max_actions": 3}), (KeyError, statuses[0], bad, {}),
+                             (KeyError, statuses[0], no_active, {}), (ZeroDivisionError, zero, cases[0]["request"], {})):
+        if req is no_active and req.get("forceSwitch"):
+            continue
+        with pytest.raises(exc):
+            P.pack_request_into_py(buf, 0, bs, req, tables, **kw)
+        with pytest.raises(exc):
+            c_call(buf, 0, bs, req, **kw)
+    with pytest.raises(ValueError):
+        c_call(bytearray(100), 0, statuses[0], cases[0]["request"])      # the record does not fit the buffer
+    assert P.pack_request_into is not None
+
+
 def test_get_possible_actions_equals_reference(cases, tables):
     """the restated get_possible_actions against the reference's outputs, field by field"""
     from pokeai_b200.protocol import get_possible_actions

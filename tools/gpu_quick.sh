@@ -1,13 +1,9 @@
 #!/bin/bash
 set -u
-OUT=gpurun_out
-mkdir -p $OUT
-echo "== pytest update"; timeout 900 python -m pytest tests/test_gpu_update.py tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -3
-for NB in 32768 4096; do echo "== bench_update --batch $NB"; timeout 300 python bench_update.py --cpu-seconds 0 --steps 100 --batch $NB | python -c "
+python -m pokeai_b200.build | tail -1
+echo "== pytest lockstep/protocol"; timeout 600 python -m pytest tests/test_lockstep.py tests/test_protocol.py -x -q 2>&1 | tail -3
+for P in 0 1; do echo "== PK_PY_PACKER=$P"; PK_PY_PACKER=$P timeout 600 python bench.py --steps 5 --warmup 3 --cpu-seconds 0 --no-e2e --skip-legs shard65536,dense,update,wide_update,gpu_reference,wide | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['value'], d['ms_per_step'])"; done
-echo "== launches"; timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/r02_launches_update.csv python bench_update.py --cpu-seconds 0 --steps 3 --warmup 3 > /dev/null 2>&1; python - <<'PY'
-import csv
-rows=[r for r in csv.reader(open('gpurun_out/r02_launches_update.csv')) if len(r)>10 and r[0].isdigit()]
-for r in rows[-8:]: print(r[4][:60], r[-1])
-PY
+d=json.loads(sys.stdin.read().strip().splitlines()[-1])
+for r in d['roofline']['secondary']: print({k:(round(v,2) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','decisions_per_s','round_trip_us','host_pack_us_per_round','gpu_call_us_per_round','cpu_reference_round_us','error')})"
+done
