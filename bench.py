@@ -403,7 +403,7 @@ def b200_arm(args, rank, local_rank, world):
         barrier()
         te0 = time.perf_counter()
         for i in range(n_sync):
-            a = agent.act_batch(host_recs[i % n_rot])  # pack into pinned staging, H2D, kernel, D2H, sync
+            a = agent.act_batch(host_recs[i % n_rot])  # pageable records: H2D copy, kernel, results to pinned memory, sync
         torch.cuda.synchronize()
         te = max_over_ranks(time.perf_counter() - te0)
         barrier()
@@ -453,7 +453,8 @@ def b200_arm(args, rank, local_rank, world):
                "pageable_input_api": "the same with the records in ordinary host memory: one more 590 KB host copy into "
                                      "pinned staging per launch",
                "sync_value": B * world * n_sync / te, "sync_ms_per_launch": te / n_sync * 1e3,
-               "sync_api": f"AgentVal.act_batch(packed records): one blocking call per launch ({n_sync} calls timed)"}
+               "sync_api": f"AgentVal.act_batch(packed records in pageable host memory): one blocking call per launch "
+                           f"({n_sync} calls timed; 61 us per call with the records in pinned_records(), tools/prof_act_batch.py)"}
     sampler.stop()
 
     # ---- the other BASELINE configurations, same process (bench_secondary.py) -> roofline.secondary ------------------

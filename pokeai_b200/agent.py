@@ -18,6 +18,7 @@ import torch
 
 from . import _native as N
 from .feature_extractor import FeatureExtractor
+from .packed import PK_OBS_DTYPE
 from .replay_buffer import ReplayBuffer, ReplayBufferItem
 
 logger = getLogger(__name__)
@@ -107,12 +108,16 @@ class Agent:
                 spec = SelectSpec(mode, eps, temperature, ue, up)
             return self._wide.decide(rec, spec)
         s = self._session(n)
-        self._feature_extractor.pack(obs_list, out=s.packed)
+        direct = None
+        if isinstance(obs_list, np.ndarray) and obs_list.dtype == PK_OBS_DTYPE and obs_list.flags.c_contiguous:
+            direct = obs_list  # already packed: read in place (no 144 B x n host copy into the staging buffer)
+        else:
+            self._feature_extractor.pack(obs_list, out=s.packed)
         if mode == N.PK_SELECT_EPSGREEDY:
             s.u_explore[:n] = u_explore
         if mode != N.PK_SELECT_ARGMAX:
             s.u_pick[:n] = u_pick
-        return s.decide(n, mode, eps, temperature)
+        return s.decide(n, mode, eps, temperature, packed=direct)
 
     def act_batch(self, obs_list) -> np.ndarray:
         """Greedy decisions for a batch: q[mask == 0] = -inf; argmax (agent.py:32-35)."""

@@ -95,13 +95,19 @@ class DecisionSession:
             self._weights_key = key
 
     def decide(self, B: int, mode: int = N.PK_SELECT_ARGMAX, eps: float = 0.0,
-               temperature: float = 1.0) -> Tuple[np.ndarray, np.ndarray]:
-        """Run the first B staged records.  Returns views (q (B, A), action (B,)) of the pinned
-        result buffers, valid until the next call."""
+               temperature: float = 1.0, packed: Optional[np.ndarray] = None) -> Tuple[np.ndarray, np.ndarray]:
+        """Run the first B staged records -- or, with `packed`, the first B records of that C-contiguous PK_OBS_DTYPE
+        array, read in place (zero-copy over PCIe when it is pinned, see `pinned_records`; a driver-side copy when it is
+        pageable).  Returns views (q (B, A), action (B,)) of the pinned result buffers, valid until the next call."""
         if not 0 <= B <= self.max_batch:
             raise ValueError(f"batch {B} exceeds the session capacity {self.max_batch}")
+        src = self._pin_packed.data_ptr()
+        if packed is not None:
+            if packed.dtype != PK_OBS_DTYPE or not packed.flags.c_contiguous or len(packed) < B:
+                raise ValueError("packed must be a C-contiguous PK_OBS_DTYPE array of at least B records")
+            src = packed.ctypes.data
         N.check(N.lib().pk_session_decide_host(
-            self._h, self._pin_packed.data_ptr(), B, int(mode), float(eps), float(temperature),
+            self._h, src, B, int(mode), float(eps), float(temperature),
             self._pin_u.data_ptr(), self._pin_u.data_ptr() + 4 * self.max_batch,
             self._pin_q.data_ptr(), self._pin_action.data_ptr()))
         return self.q[:B], self.action[:B]

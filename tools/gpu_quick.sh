@@ -1,9 +1,6 @@
 #!/bin/bash
-set -u
-python -m pokeai_b200.build | tail -1
-echo "== pytest lockstep/protocol"; timeout 600 python -m pytest tests/test_lockstep.py tests/test_protocol.py -x -q 2>&1 | tail -3
-for P in 0 1; do echo "== PK_PY_PACKER=$P"; PK_PY_PACKER=$P timeout 600 python bench.py --steps 5 --warmup 3 --cpu-seconds 0 --no-e2e --skip-legs shard65536,dense,update,wide_update,gpu_reference,wide | python -c "
+for S in 4000 0; do echo "== PK_SESSION_SPIN=$S"; PK_SESSION_SPIN=$S timeout 300 python tools/prof_act_batch.py 2>&1 | grep "us per call"; done
+echo "== tests"; timeout 900 python -m pytest tests/test_gpu_agents.py tests/test_lockstep.py tests/test_gpu_decide.py -m gpu -x -q 2>&1 | tail -2
+timeout 600 python bench.py --steps 20 --warmup 5 --cpu-seconds 0 --no-secondary | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1])
-for r in d['roofline']['secondary']: print({k:(round(v,2) if isinstance(v,float) else v) for k,v in r.items() if k in ('leg','decisions_per_s','round_trip_us','host_pack_us_per_round','gpu_call_us_per_round','cpu_reference_round_us','error')})"
-done
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); e=d['e2e']; print('value', d['value'], 'e2e', e['value'], 'pageable', e['pageable_input_value'], 'sync', e['sync_value'], e['sync_ms_per_launch'])"
