@@ -66,6 +66,7 @@ struct PkGlobal {
   // side stream of the wide backward: the HBM-bound column sums run beside the tensor-bound GEMMs (PK_WIDE_SIDE)
   int wide_tma_store = 1;  // wide GEMM: bf16 outputs through shared memory + TMA stores (PK_WIDE_TMA_STORE)
   int wide_side = 1;
+  int wide_2cta = 1;  // wide GEMM: CTA-pair (cta_group::2) form for the K-major GEMMs (PK_WIDE_2CTA)
   int wide_fused_head = 1;  // pk_wide_forward: head folded into the last GEMM's epilogue (PK_WIDE_FUSED_HEAD)
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -140,6 +141,7 @@ extern "C" int pk_init(const pk_tables* t, int device) {
   g.dense_warps = env_int("PK_DENSE_WARPS", 16, 1, 16);
   g.wide_side = env_int("PK_WIDE_SIDE", 1, 0, 1);
   g.wide_fused_head = env_int("PK_WIDE_FUSED_HEAD", 1, 0, 1);
+  g.wide_2cta = env_int("PK_WIDE_2CTA", 1, 0, 1);
   g.wide_tma_store = env_int("PK_WIDE_TMA_STORE", 1, 0, 1);
   g.decide_pair = env_int("PK_DECIDE_PAIR", 1, 0, 2);  // 0 never, 1 when features are not written, 2 always
   g.decide_tc = env_int("PK_DECIDE_TC", 0, 0, 2);

@@ -55,6 +55,56 @@ __device__ __forceinline__ void pkw_tma_store_2d(const CUtensorMap* map, const v
                "r"(pk_smem_u32(ssrc)), "r"(c0), "r"(c1)
                : "memory");
 }
+// ---- CTA-pair (cta_group::2) forms: two CTAs of a cluster on adjacent SMs run ONE MMA over 256 rows -----------------
+#define PKW_PEER_MASK 0xFEFFFFFFu  // clears the CTA-rank bit of a shared::cluster address: the pair's even (leader) CTA
+__device__ __forceinline__ uint32_t pkw_cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void pkw_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");  // not .aligned: lanes 0 of the producer / MMA warps arrive apart from their warps
+}
+// TMA load whose byte count is credited to the LEADER CTA's mbarrier (same offset in the leader's shared memory)
+__device__ __forceinline__ void pkw_tma_load_2d_pair(void* sdst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          pk_smem_u32(sdst)),
+      "l"(map), "r"(pk_smem_u32(bar) & PKW_PEER_MASK), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void pkw_mma_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// arrives on the barrier at this offset in BOTH CTAs of the pair once every MMA issued so far has completed
+__device__ __forceinline__ void pkw_mma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   pk_smem_u32(bar)),
+               "h"((unsigned short)3)
+               : "memory");
+}
+// arrive on the LEADER CTA's barrier at this offset (from either CTA of the pair)
+__device__ __forceinline__ void pkw_mbar_arrive_leader(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, 0;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(pk_smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void pkw_tmem_alloc_pair(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(pk_smem_u32(slot)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void pkw_tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+#define PKW_STAGES2 5  // CTA-pair form: a stage is A 16 KB + half of B 16 KB
+#define PKW_SMEM_BYTES2 (PKW_STAGES2 * (PKW_A_BYTES + PKW_B_BYTES / 2) + PKW_OUT_BYTES + 1024 + 256)
+
 __device__ __forceinline__ void pkw_prefetch_map(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -143,25 +193,36 @@ struct PkwGemmArgs {
 // MN == 0:  Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
 // MN == 1:  Y (M, N) = A (K, M)^T . W (K, N): both operands bf16 row-major with the CONTRACTION index as the row
 //           (weight gradient dW = dZ^T H); the tensor maps then have 64 x 64 boxes.
-template <int MN>
+// CG == 2 (MN == 0 only): launched as clusters of two CTAs.  A pair works on a 256-row x 256-column tile: each CTA loads
+// its 128 rows of A and HALF of the weight tile (128 of its 256 rows), the leader CTA issues one cta_group::2 MMA per
+// K step over both halves, and each CTA's epilogue drains its own 128 accumulator rows.  Per CTA the weight tile costs
+// half the shared-memory traffic and half the TMA bytes of the CG == 1 form.
+template <int MN, int CG = 1>
 __global__ void __launch_bounds__(PKW_THREADS, 1)
 pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_o, PkwGemmArgs g) {
+  static_assert(CG == 1 || MN == 0, "the CTA-pair form is built for K-major operands");
+  constexpr int STAGES = CG == 2 ? PKW_STAGES2 : PKW_STAGES;
+  constexpr uint32_t B_BYTES = PKW_B_BYTES / CG;            // this CTA's part of the weight tile
+  constexpr uint32_t STAGE_BYTES = PKW_A_BYTES + B_BYTES;
+  constexpr int TILE_M = PKW_BM * CG;                       // rows of an output tile (per CTA: PKW_BM)
+  const int crank = CG == 2 ? (int)pkw_cluster_ctarank() : 0;
+  const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, n_units = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   // SWIZZLE_128B tiles need 1024-byte alignment: asked for in the declaration, so that the accesses stay in the shared
   // address space (STS / LDS instead of generic stores and loads)
   extern __shared__ __align__(1024) unsigned char pkw_smem[];
   unsigned char* smem = pkw_smem;
   if ((pk_smem_u32(smem) & 1023u) != 0u) __trap();
   unsigned char* tiles = smem;
-  unsigned char* out_stage = smem + PKW_STAGES * PKW_STAGE_BYTES;  // 1024-byte aligned: SWIZZLE_64B staging
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + PKW_STAGES * PKW_STAGE_BYTES + PKW_OUT_BYTES);
-  uint64_t* empty = full + PKW_STAGES;
-  uint64_t* tfull = empty + PKW_STAGES;
+  unsigned char* out_stage = smem + STAGES * STAGE_BYTES;  // 1024-byte aligned: SWIZZLE_64B staging
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + PKW_OUT_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_mblk = (g.M + PKW_BM - 1) / PKW_BM, n_nblk = (g.N + PKW_BN - 1) / PKW_BN,
+  const int n_mblk = (g.M + TILE_M - 1) / TILE_M, n_nblk = (g.N + PKW_BN - 1) / PKW_BN,
             n_kblk = (g.K + PKW_BK - 1) / PKW_BK;
   const int n_mn = n_mblk * n_nblk;
   const int n_tiles = n_mn * g.ksplit;                      // tile = split * n_mn + mb * n_nblk + nb
@@ -171,19 +232,23 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     pkw_prefetch_map(&map_a);
     pkw_prefetch_map(&map_w);
     if (g.tma_store) pkw_prefetch_map(&map_o);
-    for (int i = 0; i < PKW_STAGES; ++i) {
+    for (int i = 0; i < STAGES; ++i) {
       pk_mbar_init(full + i, 1);
       pk_mbar_init(empty + i, 1);
     }
     for (int i = 0; i < 2; ++i) {
       pk_mbar_init(tfull + i, 1);
-      pk_mbar_init(tempty + i, PKW_EPI_WARPS);
+      pk_mbar_init(tempty + i, PKW_EPI_WARPS * CG);  // pair form: both CTAs' epilogue warps arrive on the leader's
     }
     pk_fence_mbar_init();
   }
-  if (warp == 1) pkw_tmem_alloc(tmem_slot, 512);
+  if (warp == 1) {
+    if constexpr (CG == 2) pkw_tmem_alloc_pair(tmem_slot, 512);
+    else pkw_tmem_alloc(tmem_slot, 512);
+  }
   pkw_tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) pkw_cluster_sync();  // both CTAs' barriers exist before anything arrives on them remotely
+  else __syncthreads();
   pkw_tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -191,14 +256,25 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     // ===== TMA producer =====
     int s = 0;
     uint32_t ph = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (int tile = unit; tile < n_tiles; tile += n_units) {
       const int sp = tile / n_mn, mn = tile - sp * n_mn;
       const int mb = mn / n_nblk, nb = mn - mb * n_nblk;
       const int kb0 = sp * kps, kb1 = min(n_kblk, kb0 + kps);
       for (int kb = kb0; kb < kb1; ++kb) {
         pk_mbar_wait(empty + s, ph ^ 1u);
-        pk_mbar_expect_tx(full + s, PKW_STAGE_BYTES);
-        unsigned char* sa = tiles + s * PKW_STAGE_BYTES;
+        unsigned char* sa = tiles + s * STAGE_BYTES;
+        if constexpr (CG == 2) {
+          // the leader's barrier counts both CTAs' bytes; each CTA brings its rows of A and its half of the weights
+          if (crank == 0) pk_mbar_expect_tx(full + s, 2u * STAGE_BYTES);
+          pkw_tma_load_2d_pair(sa, &map_a, kb * PKW_BK, mb * TILE_M + crank * PKW_BM, full + s);
+          pkw_tma_load_2d_pair(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN + crank * (PKW_BN / 2), full + s);
+          if (++s == STAGES) {
+            s = 0;
+            ph ^= 1u;
+          }
+          continue;
+        }
+        pk_mbar_expect_tx(full + s, STAGE_BYTES);
         if constexpr (MN == 0) {
           pkw_tma_load_2d(sa, &map_a, kb * PKW_BK, mb * PKW_BM, full + s);
           pkw_tma_load_2d(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN, full + s);
@@ -210,19 +286,19 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           for (int j = 0; j < PKW_BN / 64; ++j)
             pkw_tma_load_2d(sa + PKW_A_BYTES + j * 8192, &map_w, nb * PKW_BN + 64 * j, kb * PKW_BK, full + s);
         }
-        if (++s == PKW_STAGES) {
+        if (++s == STAGES) {
           s = 0;
           ph ^= 1u;
         }
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1 && lane == 0 && crank == 0) {
     // ===== MMA issuer =====
-    constexpr uint32_t idesc = pkw_instr_desc(PKW_BM, PKW_BN, MN);
+    constexpr uint32_t idesc = pkw_instr_desc(TILE_M, PKW_BN, MN);
     int s = 0;
     uint32_t ph = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (int tile = unit; tile < n_tiles; tile += n_units, ++it) {
       const int as = it & 1;
       const uint32_t aph = (uint32_t)(it >> 1) & 1u;
       pk_mbar_wait(tempty + as, aph ^ 1u);  // the epilogue has drained this accumulator
@@ -233,22 +309,30 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       for (int kb = kb0; kb < kb1; ++kb) {
         pk_mbar_wait(full + s, ph);
         pkw_tc_fence_after();
-        const uint32_t sa = pk_smem_u32(tiles + s * PKW_STAGE_BYTES);
+        const uint32_t sa = pk_smem_u32(tiles + s * STAGE_BYTES);
         const uint64_t adesc = MN ? pkw_smem_desc_mn128(sa) : pkw_smem_desc_k128(sa);
         const uint64_t bdesc = MN ? pkw_smem_desc_mn128(sa + PKW_A_BYTES) : pkw_smem_desc_k128(sa + PKW_A_BYTES);
         // UMMA_K = 16: K-major advances 16 bf16 = 32 B inside the swizzle atom (+2 in the 16-byte address field),
         // MN-major advances 16 k-rows of 128 B = 2048 B (+128)
         constexpr uint64_t kstep = MN ? 128u : 2u;
 #pragma unroll
-        for (int k = 0; k < PKW_BK / 16; ++k)
-          pkw_mma(d_tmem, adesc + kstep * (uint64_t)k, bdesc + kstep * (uint64_t)k, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
-        pkw_mma_commit(empty + s);  // frees the stage once these MMAs have read it
-        if (++s == PKW_STAGES) {
+        for (int k = 0; k < PKW_BK / 16; ++k) {
+          if constexpr (CG == 2)
+            pkw_mma_pair(d_tmem, adesc + kstep * (uint64_t)k, bdesc + kstep * (uint64_t)k, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+          else
+            pkw_mma(d_tmem, adesc + kstep * (uint64_t)k, bdesc + kstep * (uint64_t)k, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+        }
+        // frees the stage (in both CTAs of a pair) once these MMAs have read it
+        if constexpr (CG == 2) pkw_mma_commit_pair(empty + s);
+        else pkw_mma_commit(empty + s);
+        if (++s == STAGES) {
           s = 0;
           ph ^= 1u;
         }
       }
-      pkw_mma_commit(tfull + as);  // accumulator complete
+      // accumulator complete (each CTA of a pair holds its 128 rows)
+      if constexpr (CG == 2) pkw_mma_commit_pair(tfull + as);
+      else pkw_mma_commit(tfull + as);
     }
   } else if (warp >= 2) {
     // ===== epilogue: TMEM -> registers -> bias, ReLU -> global =====
@@ -264,7 +348,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     unsigned char* my_stage = out_stage + (warp - 2) * (2 * PKW_OUT_STAGE_BYTES);
     int sbuf = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (int tile = unit; tile < n_tiles; tile += n_units, ++it) {
       const int sp = tile / n_mn, mn = tile - sp * n_mn;
       const int mb = mn / n_nblk, nb = mn - mb * n_nblk;
       float* const out_f32 = g.out_f32 != nullptr ? g.out_f32 + (size_t)sp * g.M * g.N : nullptr;
@@ -272,7 +356,8 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       const uint32_t aph = (uint32_t)(it >> 1) & 1u;
       pk_mbar_wait(tfull + as, aph);
       pkw_tc_fence_after();
-      const int row = mb * PKW_BM + quarter * 32 + lane;
+      const int row0 = mb * TILE_M + crank * PKW_BM + quarter * 32;  // first row of this warp's TMEM lane quarter
+      const int row = row0 + lane;
       const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * PKW_BN);
       float hs0 = 0.0f, hs1 = 0.0f, hs2 = 0.0f, hs3 = 0.0f;  // fused head: this row's partial over the warp's columns
 #pragma unroll 1
@@ -343,7 +428,7 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           pk_fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            pkw_tma_store_2d(&map_o, st, n0, mb * PKW_BM + quarter * 32);
+            pkw_tma_store_2d(&map_o, st, n0, row0);
             pk_bulk_commit();
           }
           sbuf ^= 1;
@@ -375,15 +460,20 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         g.head_part[(size_t)row * (2 * n_nblk) + 2 * nb + ((warp - 2) >> 2)] = (hs0 + hs1) + (hs2 + hs3);
       pkw_tc_fence_before();
       __syncwarp();
-      if (lane == 0) pkw_mbar_arrive(tempty + as);
+      if (lane == 0) {
+        if constexpr (CG == 2) pkw_mbar_arrive_leader(tempty + as);
+        else pkw_mbar_arrive(tempty + as);
+      }
     }
   }
   if (warp >= 2 && lane == 0) pk_bulk_wait_all();  // TMA stores of the last tiles (no-op when none were issued)
   pkw_tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) pkw_cluster_sync();  // the peer's shared memory and TMEM stay alive until both CTAs are done
+  else __syncthreads();
   if (warp == 1) {
     __syncwarp();
-    pkw_tmem_dealloc(tmem_base, 512);
+    if constexpr (CG == 2) pkw_tmem_dealloc_pair(tmem_base, 512);
+    else pkw_tmem_dealloc(tmem_base, 512);
   }
 }
 
