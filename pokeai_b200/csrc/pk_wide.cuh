@@ -193,7 +193,7 @@ struct PkwGemmArgs {
 // MN == 0:  Y (M, N) = act(A (M, K) . W (N, K)^T + bias): both operands bf16 row-major with K contiguous.
 // MN == 1:  Y (M, N) = A (K, M)^T . W (K, N): both operands bf16 row-major with the CONTRACTION index as the row
 //           (weight gradient dW = dZ^T H); the tensor maps then have 64 x 64 boxes.
-// CG == 2 (MN == 0 only): launched as clusters of two CTAs.  A pair works on a 256-row x 256-column tile: each CTA loads
+// CG == 2: launched as clusters of two CTAs.  A pair works on a 256-row x 256-column tile: each CTA loads
 // its 128 rows of A and HALF of the weight tile (128 of its 256 rows), the leader CTA issues one cta_group::2 MMA per
 // K step over both halves, and each CTA's epilogue drains its own 128 accumulator rows.  Per CTA the weight tile costs
 // half the shared-memory traffic and half the TMA bytes of the CG == 1 form.
@@ -201,7 +201,6 @@ template <int MN, int CG = 1>
 __global__ void __launch_bounds__(PKW_THREADS, 1)
 pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_o, PkwGemmArgs g) {
-  static_assert(CG == 1 || MN == 0, "the CTA-pair form is built for K-major operands");
   constexpr int STAGES = CG == 2 ? PKW_STAGES2 : PKW_STAGES;
   constexpr uint32_t B_BYTES = PKW_B_BYTES / CG;            // this CTA's part of the weight tile
   constexpr uint32_t STAGE_BYTES = PKW_A_BYTES + B_BYTES;
@@ -266,8 +265,18 @@ pk_wide_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         if constexpr (CG == 2) {
           // the leader's barrier counts both CTAs' bytes; each CTA brings its rows of A and its half of the weights
           if (crank == 0) pk_mbar_expect_tx(full + s, 2u * STAGE_BYTES);
-          pkw_tma_load_2d_pair(sa, &map_a, kb * PKW_BK, mb * TILE_M + crank * PKW_BM, full + s);
-          pkw_tma_load_2d_pair(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN + crank * (PKW_BN / 2), full + s);
+          if constexpr (MN == 0) {
+            pkw_tma_load_2d_pair(sa, &map_a, kb * PKW_BK, mb * TILE_M + crank * PKW_BM, full + s);
+            pkw_tma_load_2d_pair(sa + PKW_A_BYTES, &map_w, kb * PKW_BK, nb * PKW_BN + crank * (PKW_BN / 2), full + s);
+          } else {
+#pragma unroll
+            for (int j = 0; j < PKW_BM / 64; ++j)
+              pkw_tma_load_2d_pair(sa + j * 8192, &map_a, mb * TILE_M + crank * PKW_BM + 64 * j, kb * PKW_BK, full + s);
+#pragma unroll
+            for (int j = 0; j < PKW_BN / 2 / 64; ++j)
+              pkw_tma_load_2d_pair(sa + PKW_A_BYTES + j * 8192, &map_w, nb * PKW_BN + crank * (PKW_BN / 2) + 64 * j,
+                                   kb * PKW_BK, full + s);
+          }
           if (++s == STAGES) {
             s = 0;
             ph ^= 1u;
