@@ -46,6 +46,12 @@
 //     successive MMAs share an accumulator or alternate between two; two issuing warps are slower (~200).  Eight per
 //     tile and k-block = ~1 200 cycles: with the X producer (~1 400 per k-block with its waits) this is what bounds
 //     the kernel now.  Without the MMAs the kernel takes 320 us, without MMAs and TMEM stores 311 us.
+//   * a CTA-pair form (clusters of two CTAs, each with its own tiles, the leader issuing tcgen05.mma.cta_group::2 with A
+//     from both CTAs' TMEM so that one instruction covers 256 rows, each CTA staging half of every weight operand) was
+//     built and passed the parity tests, but ran at 589 us against 419 on the same box: with one A stage per tile the
+//     loop workers -> a_full -> MMA -> a_empty -> workers has no slack, and the remote arrivals and multicast commits
+//     put two cluster-scope latencies into it, with both CTAs forced into lock step.  Not kept.  (The same pairing is
+//     what lifted the wide GEMM from 83 to 93 % tensor-active: there the ring is five stages deep.)
 //   * next: X through tensor maps (four boxes per k-block instead of fourteen bulk loads) and layer 0 as bf16 x 3-way
 //     split with K = 16 per MMA (half the MMAs); neither is built.
 // Reference semantics: MLPModel.forward mlp_model.py:21-30 on Agent._calc_q_vector[_batch] input (agent.py:23-30).
