@@ -348,28 +348,52 @@ def leg_wide_update(ctx, NG=32768, nl=4, H=2048, steps=4):
         sets.append((ops.packed_to_device(s, dev), ops.packed_to_device(s2, dev), torch.from_numpy(ac).to(dev),
                      torch.from_numpy(r).to(dev), torch.from_numpy(t).to(dev)))
 
-    def step(i):
-        tr._wide_grad_device(*sets[i % 2], NG, dist if world > 1 else None)  # per-layer NCCL buckets inside at N > 1
-        tr._wide_apply()
-
-    ms = _timed(ctx, step, steps, warm=2)
-    n_par = tr._flat.numel()
-    checks = None
-    if world > 1:
-        allp = [torch.empty_like(tr._flat) for _ in range(world)]
-        dist.all_gather(allp, tr._flat)
-        checks = {"parameters_bit_identical_across_ranks": bool(all(torch.equal(allp[0], p) for p in allp))}
     fwd = H * (617 + (nl - 1) * H + 1)
     fma = 2 * 9 * fwd + fwd + fwd + (nl - 1) * H * H  # two 9-column forwards, 1-column forward, dW, dX
     pk_ = _peaks()
-    tf = 2.0 * fma * (hi - lo) / (ms * 1e-3) / 1e12
+    n_par = tr._flat.numel()
+
+    def measure(route):
+        px = tr._peer_exchange_wide(dist) if (route == "peer" and world > 1) else None
+        if route == "peer" and world > 1 and px is None:
+            return None
+
+        def step(i):
+            if px is not None:  # shard gradient straight into the exchange buffer, ONE kernel sums it over the ranks
+                grad, loss_slot = px.next_slot()
+                loss_slot.copy_(tr._wide_grad_device(*sets[i % 2], NG, None, out_grad=grad))
+                px.allreduce()
+                tr._wide_apply(grad)
+            else:
+                tr._wide_grad_device(*sets[i % 2], NG, dist if world > 1 else None)  # per-layer NCCL buckets inside at N > 1
+                tr._wide_apply()
+
+        ms = _timed(ctx, step, steps, warm=2)
+        checks = None
+        if world > 1:
+            allp = [torch.empty_like(tr._flat) for _ in range(world)]
+            dist.all_gather(allp, tr._flat)
+            checks = {"parameters_bit_identical_across_ranks": bool(all(torch.equal(allp[0], p) for p in allp))}
+            if px is not None:
+                checks["peer_timeout_flag"] = float(px.loss_status[1].item())
+        tf = 2.0 * fma * (hi - lo) / (ms * 1e-3) / 1e12
+        exch = ("none" if world == 1 else
+                "peer: sliced reduce-scatter + all-gather over NVLink peer memory in one kernel (pk_peer_allreduce), then "
+                "clamp + Adam" if px is not None else "nccl: one allreduce bucket per layer started from inside the backward")
+        return {"config": f"configs[3] on the wide net {nl}x{H}: {NG} transitions per step (global), dp{world}",
+                "scaling": "strong", "unit": "transitions/s", "transitions_per_s": NG / (ms * 1e-3), "ms_per_step": ms,
+                "steps": steps, "gradient_floats": n_par, "exchange": exch, "parity": checks,
+                "parity_ok": None if checks is None else bool(checks["parameters_bit_identical_across_ranks"]
+                                                              and checks.get("peer_timeout_flag", 0.0) == 0.0),
+                "tflops_per_gpu": tf, "frac_burst": tf / pk_["bf16_burst"], "frac_sustained": tf / pk_["bf16_sustained"]}
+
+    out = []
+    for route in (("peer", "nccl") if world > 1 else ("nccl",)):
+        r = measure(route)
+        if r is not None:
+            out.append(r)
     del tr
-    return {"config": f"configs[3] on the wide net {nl}x{H}: {NG} transitions per step (global), dp{world}",
-            "scaling": "strong", "unit": "transitions/s", "transitions_per_s": NG / (ms * 1e-3), "ms_per_step": ms,
-            "steps": steps, "gradient_floats": n_par,
-            "exchange": "none" if world == 1 else "nccl: one allreduce bucket per layer started from inside the backward",
-            "parity": checks, "tflops_per_gpu": tf, "frac_burst": tf / pk_["bf16_burst"],
-            "frac_sustained": tf / pk_["bf16_sustained"]}
+    return out
 
 
 # ---- configs[4]: wide net on the tensor cores --------------------------------------------------------------------

@@ -288,6 +288,16 @@ PK_API int pk_peer_clamp_adam(float* params, const float* const* peer_grads, uin
                        int world, uint32_t epoch, float* exp_avg, float* exp_avg_sq, int n_layers, int n_channels,
                        int in_channels, float lr, float beta1, float beta2, float eps, int step, float* prepared,
                        float* grad_sum, float* loss_status, void* stream);
+/* Sum of a LARGE gradient vector over the ranks of one NVSwitch box through peer memory, in place: the wide network's
+ * 55 MB gradient (replaces dist.all_reduce(grad) of trainer.py:192-195 at world size > 1; clamp + Adam follow with
+ * pk_clamp_adam).  Buffers, flags, epochs and the parity rule are pk_peer_clamp_adam's (flag words 0..7 "written",
+ * 8..15 "reduced", 16 a counter: >= 17 zeroed uint32 per rank).  Rank r sums slice r of the vector over all ranks in rank
+ * order and the ranks then copy each other's slices: afterwards every rank's buffer of this epoch holds the same bits.
+ * n_floats (a multiple of 4) covers everything that is to be summed (the loss share behind the gradient included).
+ * status (2 floats, may be NULL): [1] = 1.0 if a peer did not arrive within PK_PEER_TIMEOUT_MS -- the exchange object
+ * is then unusable.  Every rank must make the call, with the same grid (the library uses one CTA per SM). */
+PK_API int pk_peer_allreduce(float* const* peer_grads, uint32_t* const* peer_flags, int rank, int world, uint32_t epoch,
+                      size_t n_floats, float* status, void* stream);
 /* The same with epoch, step and the Adam constants read from a device control block (see pk_update_ctl): peer_grads
  * must be the buffer set of the parity of the epoch the graph will run at. */
 PK_API int pk_peer_clamp_adam_ctl(float* params, const float* const* peer_grads, uint32_t* const* peer_flags, int rank,

@@ -87,6 +87,7 @@ _SIGNATURES = {
     "pk_update_ctl_advance": (C.c_int, [_vp, _vp]),
     "pk_clamp_adam_ctl": (C.c_int, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "pk_peer_clamp_adam_ctl": (C.c_int, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "pk_peer_allreduce": (C.c_int, [_vp, _vp, _i, _i, C.c_uint32, C.c_size_t, _vp, _vp]),
     "pk_peer_clamp_adam": (C.c_int, [_vp, _vp, _vp, _i, _i, C.c_uint32, _vp, _vp, _i, _i, _i, _f, _f, _f, _f, _i, _vp, _vp,
                                      _vp, _vp]),
     "pk_session_create": (C.c_int, [C.POINTER(_vp), _i, _i, _i]),

@@ -558,6 +558,93 @@ __global__ void pk_peer_clamp_adam_kernel(float* __restrict__ params, PkPeers pe
   }
 }
 
+// ---- sum of a LARGE gradient over the ranks of one NVSwitch box, through peer memory (wide network: 55 MB) --------
+// pk_peer_clamp_adam_kernel reads every element from every peer on every rank: right for the 175 KB gradient of the
+// default network, W times too much traffic for the wide one.  Here the vector is cut into W slices:
+//   phase A  wait for every rank's "gradient of epoch e written" flag; rank r sums slice r over the W buffers IN RANK
+//            ORDER (16-byte system-scope loads over NVLink) and writes the sums back into ITS buffer's slice r
+//            (nobody else reads that slice of that buffer in this phase);
+//   flag     the last CTA of the grid to finish phase A (a counter that grows by gridDim.x per call) publishes
+//            "slice r of epoch e reduced" to every peer;
+//   phase B  wait for every rank's "reduced" flag and copy slice p from rank p's buffer for every p != r.
+// Afterwards every rank's buffer holds the same bits: each element was summed by exactly one rank, in rank order.
+// Buffers alternate by epoch parity exactly as for pk_peer_clamp_adam (a buffer is rewritten at epoch e + 2, when
+// every rank has left the kernel of epoch e: they all published "written e + 1" after it).  Traffic per rank:
+// 2 (W - 1) / W of the vector over NVLink instead of NCCL's ring / tree passes; one launch, no second barrier.
+// Flag words: flags[d][r] = "written", flags[d][8 + r] = "reduced", flags[rank][16] = the phase-A counter.
+// Time-out as above: a CTA that gives up raises status[1] and returns; the exchange is then unusable (the counter is
+// off) and the host must stop (Trainer raises).
+__device__ __forceinline__ float4 pk_ld_relaxed_sys_v4(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool pk_peer_wait_flags(const unsigned* f, int world, unsigned epoch, unsigned long long timeout_ns,
+                                                   int* s_timed_out) {
+  if (threadIdx.x == 0) *s_timed_out = 0;
+  __syncthreads();
+  if (threadIdx.x < (unsigned)world) {
+    const unsigned long long t0 = pk_globaltimer();
+    while ((int)(pk_ld_acquire_sys(f + threadIdx.x) - epoch) < 0) {
+      if (pk_globaltimer() - t0 > timeout_ns) {
+        *s_timed_out = 1;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  return *s_timed_out == 0;
+}
+__global__ void __launch_bounds__(512) pk_peer_allreduce_kernel(PkPeers pe, unsigned n4, float* __restrict__ status) {
+  __shared__ int s_timed_out;
+  unsigned* my_flags = pe.flags[pe.rank];
+  if (blockIdx.x == 0 && threadIdx.x < pe.world) {  // publish: this rank's gradient was written by earlier kernels
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pe.flags[threadIdx.x] + pe.rank), "r"(pe.epoch) : "memory");
+  }
+  if (!pk_peer_wait_flags(my_flags, pe.world, pe.epoch, pe.timeout_ns, &s_timed_out)) {
+    if (threadIdx.x == 0 && status != nullptr) status[1] = 1.0f;
+    return;
+  }
+  const unsigned per = (n4 + pe.world - 1) / pe.world;
+  float4* mine = reinterpret_cast<float4*>(const_cast<float*>(pe.grad[pe.rank]));
+  {  // phase A: my slice, summed over the ranks in rank order
+    const unsigned lo = per * pe.rank, hi = min(n4, lo + per);
+    for (unsigned i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < pe.world; ++r) {
+        const float4 v = pk_ld_relaxed_sys_v4(reinterpret_cast<const float4*>(pe.grad[r]) + i);
+        s.x += v.x;
+        s.y += v.y;
+        s.z += v.z;
+        s.w += v.w;
+      }
+      mine[i] = s;
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned old = atomicAdd(my_flags + 16, 1u);
+    if (old + 1u == pe.epoch * gridDim.x) {  // the last CTA of this call: the whole slice is in memory
+      __threadfence_system();
+      for (int d = 0; d < pe.world; ++d)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pe.flags[d] + 8 + pe.rank), "r"(pe.epoch) : "memory");
+    }
+  }
+  if (!pk_peer_wait_flags(my_flags + 8, pe.world, pe.epoch, pe.timeout_ns, &s_timed_out)) {
+    if (threadIdx.x == 0 && status != nullptr) status[1] = 1.0f;
+    return;
+  }
+  for (int k = 1; k < pe.world; ++k) {  // phase B: the other ranks' reduced slices, starting with the next rank
+    const int p = (pe.rank + k) % pe.world;
+    const unsigned lo = per * p, hi = min(n4, lo + per);
+    const float4* src = reinterpret_cast<const float4*>(pe.grad[p]);
+    for (unsigned i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x)
+      mine[i] = pk_ld_relaxed_sys_v4(src + i);
+  }
+}
+
 __global__ void pk_clamp_adam_kernel(float* __restrict__ params, const float* __restrict__ grad, float* __restrict__ m,
                                      float* __restrict__ v, PkParamLayout P, PkLayout lay, PkAdam h,
                                      float* __restrict__ prepared, const pk_update_ctl* __restrict__ ctl) {

@@ -122,6 +122,16 @@ class PeerGradExchange:
             prepared.data_ptr() if prepared is not None else None,
             grad_sum.data_ptr() if grad_sum is not None else None, self.loss_status.data_ptr(), stream))
 
+    def allreduce(self) -> None:
+        """Sum this epoch's buffer (gradient + loss share, as written through `next_slot()`) over the ranks, in place on
+        every rank: the sliced reduce-scatter / all-gather of pk_peer_allreduce (wide network).  `loss_status[1]` is
+        raised when a peer did not arrive in time; the exchange is unusable afterwards."""
+        from . import _native as N
+        assert self.epoch >= 1, "next_slot() first"
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(N.lib().pk_peer_allreduce(self._grad_ptrs[self.epoch & 1], self._flag_ptrs, self.rank, self.world,
+                                          self.epoch, self.npad, self.loss_status.data_ptr(), stream))
+
     # ---- graph-replayable form (pk_update_ctl) ------------------------------------------------------------------
     def slot(self, parity: int) -> Tuple[torch.Tensor, torch.Tensor]:
         """(gradient, loss share) views of this rank's buffer of the given epoch parity (fixed addresses: what a

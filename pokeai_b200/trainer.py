@@ -365,6 +365,16 @@ class Trainer:
         self.model.mark_updated(self._prepared)  # trainer.model(x) / Agent(trainer.model, fe) see the new weights
         return float(self._loss.item())
 
+    def _peer_exchange_wide(self, dist):
+        """PeerGradExchange for the wide network's 55 MB gradient (sliced pk_peer_allreduce), created collectively on
+        the first distributed update; None when unavailable or switched off (PK_PEER_ALLREDUCE=0): per-layer NCCL buckets."""
+        if dist is None or not self._wide:
+            return None
+        if "_pxw" not in self.__dict__:
+            from .dist import PeerGradExchange
+            self._pxw = PeerGradExchange.create(self._flat.numel(), self.device)
+        return self._pxw
+
     def _peer_exchange(self, dist):
         """PeerGradExchange of the default (small) network when a NCCL group is active and the box maps peer memory;
         created collectively on the first distributed update, None otherwise (then: NCCL allreduce)."""
@@ -375,7 +385,7 @@ class Trainer:
             self._px = PeerGradExchange.create(self._flat.numel(), self.device)
         return self._px
 
-    def _wide_grad_device(self, s_d, s2_d, a_d, r_d, t_d, n_global: int, dist=None):
+    def _wide_grad_device(self, s_d, s2_d, a_d, r_d, t_d, n_global: int, dist=None, out_grad=None):
         """Device-resident part of the wide update: fills self._grad, returns the loss tensor (1,).
         With `dist` (an active NCCL group) the gradient is also summed over ranks, one bucket per layer, each started as
         soon as that layer's slice is complete, so the 55 MB exchange overlaps the backward of the earlier layers
@@ -393,7 +403,8 @@ class Trainer:
         dq, loss = wide.dqn_dq(q_sa, q_no if self.double_dqn else None, q_nt, m2, r_d, t_d, n_global, self.gamma,
                                self.double_dqn)
         if dist is None:
-            wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq, out_grad=self._grad, chosen_only=True)
+            wide.train_backward(self._prepared, self._nl, self._H, n, A, ws, dq,
+                                out_grad=self._grad if out_grad is None else out_grad, chosen_only=True)
             return loss
         if getattr(self, "_wide_events", None) is None:
             self._wide_events = [torch.cuda.Event() for _ in range(self._nl)]
@@ -413,11 +424,12 @@ class Trainer:
         main.wait_stream(comm)
         return loss
 
-    def _wide_apply(self) -> None:
+    def _wide_apply(self, grad=None) -> None:
         """clamp + Adam on the flat parameters, then the bf16 / transposed weight copies are re-derived"""
         opt = self.optimizer
         opt.step_count += 1
-        N.check(N.lib().pk_clamp_adam(self._flat.data_ptr(), self._grad.data_ptr(), opt.exp_avg.data_ptr(),
+        grad = self._grad if grad is None else grad
+        N.check(N.lib().pk_clamp_adam(self._flat.data_ptr(), grad.data_ptr(), opt.exp_avg.data_ptr(),
                                       opt.exp_avg_sq.data_ptr(), self._nl, self._H, self._C, opt.lr, opt.betas[0],
                                       opt.betas[1], opt.eps, opt.step_count, None,
                                       torch.cuda.current_stream(self.device).cuda_stream))
@@ -443,6 +455,23 @@ class Trainer:
             t_d = torch.from_numpy(np.ascontiguousarray(terminal, dtype=np.uint8)).to(dev)
         dist = self._dist()
         nccl = dist is not None and dist.get_backend() == "nccl"
+        px = self._peer_exchange_wide(dist) if nccl else None
+        if px is not None:
+            # peer-memory route: the shard gradient is written straight into the exchange buffer of this epoch, ONE kernel
+            # sums it over the ranks in place (pk_peer_allreduce: every element summed by one rank, in rank order), and
+            # clamp + Adam run on the summed buffer; no NCCL call in the step
+            grad, loss_slot = px.next_slot()
+            if n > 0:
+                loss_slot.copy_(self._wide_grad_device(s_d, s2_d, a_d, r_d, t_d, n_global, None, out_grad=grad))
+            else:
+                grad.zero_()
+                loss_slot.zero_()
+            px.allreduce()
+            self._wide_apply(grad)
+            if float(px.loss_status[1].item()) != 0.0:
+                raise RuntimeError("peer gradient exchange: a rank did not arrive within the time limit "
+                                   "(PK_PEER_TIMEOUT_MS); the parameters of this rank are no longer in step")
+            return float(loss_slot.item())
         if n > 0:
             # NCCL group: the gradient is reduced bucket by bucket inside, overlapped with the backward
             loss = self._wide_grad_device(s_d, s2_d, a_d, r_d, t_d, n_global, dist if nccl else None)

@@ -342,3 +342,5 @@ def test_wide_overlapped_exchange_two_gpus():
                         "--master-addr", "127.0.0.1", "--master-port", "29583", str(root / "tools" / "check_wide_overlap.py")],
                        capture_output=True, text=True, timeout=600, cwd=root)
     assert r.returncode == 0 and "wide overlap ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    # the same run also checks the peer-memory route (pk_peer_allreduce) where peer mapping is available
+    assert "wide peer allreduce ok" in r.stdout or "wide peer allreduce skipped" in r.stdout, r.stdout[-2000:]

@@ -50,6 +50,44 @@ def main():
     dist.barrier()
     if rank == 0:
         print(f"wide overlap ok: world {world}, 3 steps, max |bucketed - monolithic| / max|g| = {worst:.2e}")
+    # peer-memory route (pk_peer_allreduce: sliced reduce-scatter / all-gather over NVLink, one kernel): the summed
+    # gradient must equal NCCL's within summation order, and be BIT-identical on every rank
+    px = tr._peer_exchange_wide(dist)
+    if px is None:
+        if rank == 0:
+            print("wide peer allreduce skipped: peer memory not available")
+    else:
+        worst_p = 0.0
+        for it in range(4):  # both buffer parities, twice
+            rng = np.random.default_rng(70 + it)
+            rs = synth_packed(n, seed=120 + it, party_size=6, kind="ragged", tables=T)
+            rn = synth_packed(n, seed=160 + it, party_size=6, kind="ragged", tables=T)
+            a = torch.from_numpy((rng.random(n) * rs["n_act"]).astype(np.int32)[lo:hi]).to(dev)
+            r = torch.from_numpy(rng.uniform(-1, 1, n).astype(np.float32)[lo:hi]).to(dev)
+            t = torch.from_numpy((rng.random(n) < 0.05).astype(np.uint8)[lo:hi]).to(dev)
+            s, s2 = ops.packed_to_device(rs[lo:hi], dev), ops.packed_to_device(rn[lo:hi], dev)
+            loss = tr._wide_grad_device(s, s2, a, r, t, n, None)
+            want = tr._grad.clone()
+            want_loss = loss.clone()
+            dist.all_reduce(want)
+            dist.all_reduce(want_loss)
+            grad, loss_slot = px.next_slot()
+            loss_slot.copy_(tr._wide_grad_device(s, s2, a, r, t, n, None, out_grad=grad))
+            px.allreduce()
+            torch.cuda.synchronize()
+            assert float(px.loss_status[1].item()) == 0.0, "peer allreduce timed out"
+            scale = float(want.abs().max())
+            d = float((grad - want).abs().max())
+            worst_p = max(worst_p, d / scale)
+            assert d <= 1e-5 * scale, (it, d, scale)
+            assert abs(float(loss_slot.item()) - float(want_loss.item())) < 1e-6
+            gathered = [torch.empty_like(grad) for _ in range(world)]
+            dist.all_gather(gathered, grad.contiguous())
+            assert all(torch.equal(gathered[0], g) for g in gathered), "peer allreduce: ranks disagree"
+        dist.barrier()
+        if rank == 0:
+            print(f"wide peer allreduce ok: world {world}, 4 steps, bit-identical across ranks, "
+                  f"max |peer - nccl| / max|g| = {worst_p:.2e}")
     dist.destroy_process_group()
 
 
