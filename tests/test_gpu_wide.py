@@ -344,3 +344,4 @@ def test_wide_overlapped_exchange_two_gpus():
     assert r.returncode == 0 and "wide overlap ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
     # the same run also checks the peer-memory route (pk_peer_allreduce) where peer mapping is available
     assert "wide peer allreduce ok" in r.stdout or "wide peer allreduce skipped" in r.stdout, r.stdout[-2000:]
+    assert "wide trainer peer route ok" in r.stdout or "wide peer allreduce skipped" in r.stdout, r.stdout[-2000:]

@@ -88,6 +88,41 @@ def main():
         if rank == 0:
             print(f"wide peer allreduce ok: world {world}, 4 steps, bit-identical across ranks, "
                   f"max |peer - nccl| / max|g| = {worst_p:.2e}")
+        # Trainer._update_wide end to end by both routes from the same start (a second trainer with the peer route off):
+        # same loss, parameters within summation order, identical on every rank; one rank gets an EMPTY shard once
+        import os as _os
+        _os.environ["PK_PEER_ALLREDUCE"] = "0"
+        torch.manual_seed(0)
+        tn = Trainer({"n_layers": 4, "n_channels": 2048, "bn": False}, {"batch_size": n, "lr": 1e-4}, {"party_size": 6},
+                     device=dev)
+        assert tn._peer_exchange_wide(dist) is None  # decided (and cached) while the switch is off: NCCL buckets
+        _os.environ["PK_PEER_ALLREDUCE"] = "1"
+        tn._flat.copy_(tr._flat)
+        tn.optimizer.exp_avg.copy_(tr.optimizer.exp_avg)
+        tn.optimizer.exp_avg_sq.copy_(tr.optimizer.exp_avg_sq)
+        tn.optimizer.step_count = tr.optimizer.step_count
+        tn._refresh_prepared()
+        tr._refresh_prepared()
+        for it in range(3):
+            rng = np.random.default_rng(700 + it)
+            rs = synth_packed(n, seed=220 + it, party_size=6, kind="ragged", tables=T)
+            rn = synth_packed(n, seed=260 + it, party_size=6, kind="ragged", tables=T)
+            a = (rng.random(n) * rs["n_act"]).astype(np.int32)
+            r = rng.uniform(-1, 1, n).astype(np.float32)
+            t = (rng.random(n) < 0.05).astype(np.uint8)
+            l2, h2 = (lo, hi) if not (it == 1 and rank == world - 1) else (hi, hi)  # an empty shard on the last rank
+            lp = tr._update_from_arrays(rs[l2:h2], rn[l2:h2], a[l2:h2], r[l2:h2], t[l2:h2], n_global=n)
+            ln = tn._update_from_arrays(rs[l2:h2], rn[l2:h2], a[l2:h2], r[l2:h2], t[l2:h2], n_global=n)
+            assert abs(lp - ln) < 1e-6, (it, lp, ln)
+        assert tn._peer_exchange_wide(dist) is None and tr._peer_exchange_wide(dist) is not None
+        dpar = float((tr._flat - tn._flat).abs().max())
+        assert dpar <= 1e-6, dpar
+        gathered = [torch.empty_like(tr._flat) for _ in range(world)]
+        dist.all_gather(gathered, tr._flat)
+        assert all(torch.equal(gathered[0], g) for g in gathered)
+        dist.barrier()
+        if rank == 0:
+            print(f"wide trainer peer route ok: 3 updates (one with an empty shard), max |peer - nccl| parameter = {dpar:.2e}")
     dist.destroy_process_group()
 
 
