@@ -305,6 +305,37 @@ PK_API int pk_peer_clamp_adam_ctl(float* params, const float* const* peer_grads,
                            int n_channels, int in_channels, float* prepared, float* grad_sum, float* loss_status,
                            void* stream);
 
+/* ---- train-mode BatchNorm update: MLPModel(bn=True) under Trainer._update -----------------------------------------
+ * Replaces torch autograd through Conv1d(k=1, bias=False) -> BatchNorm1d (training) -> ReLU, n_layers times, then
+ * Conv1d to one channel (pokeai/ai/generic_move_model/mlp_model.py:12-15,21-30) as the reference's Trainer runs it:
+ * Trainer.model and Trainer.target_model are never put in eval mode (trainer.py:41-43), so every forward of the update
+ * (trainer.py:163,174-175,181-182) normalises with the statistics of ITS batch -- per channel over batch x action columns,
+ * biased variance, eps 1e-5 -- and moves the running statistics (momentum 0.1, unbiased variance).
+ * `params`: the flat vector in MLPModel.parameters() order (layers.*.weight, bn_layers.*.weight / .bias per layer,
+ * output.weight, output.bias; pk_bn_param_floats floats).  `running`: [n_layers][2][n_channels] (running_mean,
+ * running_var), updated in place; NULL leaves it alone.  `feat`: dense (B, in_channels, A) features (pk_encode).
+ * `ws`: pk_bn_workspace_floats(...) floats, 16-byte aligned; it keeps every layer's pre-norm and post-ReLU activations
+ * for pk_bn_backward.  q: (B, A).  Plain FP32 kernels (every recorded run of the reference has bn = false). */
+PK_API size_t pk_bn_param_floats(int n_layers, int n_channels, int in_channels);
+PK_API size_t pk_bn_workspace_floats(int n_layers, int n_channels, int B, int A);
+PK_API size_t pk_bn_backward_scratch_floats(int n_layers, int n_channels, int B, int A);
+PK_API int pk_bn_forward_train(const float* params, float* running, int n_layers, int n_channels, int in_channels,
+                        const float* feat, int B, int A, float* ws, float* q, void* stream);
+/* Double-DQN target, smooth-L1 loss (mean over n_global) and d loss / d q (trainer.py:163-187).  slot[i] = row of
+ * transition i's next state in the COMPACTED non-final arrays q_next_online / q_next_target / mask_next (the reference
+ * forwards only the non-final next states, trainer.py:157-158), -1 when terminal.  dq: (n, A), zero except at action[i].
+ * q_next_online may be NULL when double_dqn == 0. */
+PK_API int pk_bn_dqn_dq(const float* q, const int32_t* action, const float* reward, const int32_t* slot,
+                 const float* q_next_online, const float* q_next_target, const int32_t* mask_next, int n, int A,
+                 int n_global, float gamma, int double_dqn, float* dq, float* loss, void* stream);
+/* loss.backward() (trainer.py:192) through the network pk_bn_forward_train just ran on `feat` with `ws`: the flat gradient
+ * in `params` order (not clamped).  scratch: pk_bn_backward_scratch_floats(...) floats, 16-byte aligned. */
+PK_API int pk_bn_backward(const float* params, int n_layers, int n_channels, int in_channels, const float* feat, int B,
+                   int A, const float* ws, const float* dq, float* scratch, float* grad, void* stream);
+/* pk_clamp_adam over a plain vector of n floats (no prepared copies): clamp to [-1, 1], Adam (trainer.py:193-195). */
+PK_API int pk_clamp_adam_flat(float* params, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
+                       float beta1, float beta2, float eps, int step, void* stream);
+
 /* ---- host-buffer session (for non-torch callers, and the end-to-end measurement) ------
  * Owns device buffers for up to max_batch observations and one stream.  *_host calls copy
  * packed observations host->device, run pk_decide, copy q / action back and synchronise. */

@@ -90,6 +90,13 @@ _SIGNATURES = {
     "pk_peer_allreduce": (C.c_int, [_vp, _vp, _i, _i, C.c_uint32, C.c_size_t, _vp, _vp]),
     "pk_peer_clamp_adam": (C.c_int, [_vp, _vp, _vp, _i, _i, C.c_uint32, _vp, _vp, _i, _i, _i, _f, _f, _f, _f, _i, _vp, _vp,
                                      _vp, _vp]),
+    "pk_bn_param_floats": (_sz, [_i, _i, _i]),
+    "pk_bn_workspace_floats": (_sz, [_i, _i, _i, _i]),
+    "pk_bn_backward_scratch_floats": (_sz, [_i, _i, _i, _i]),
+    "pk_bn_forward_train": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp]),
+    "pk_bn_dqn_dq": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _vp]),
+    "pk_bn_backward": (C.c_int, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "pk_clamp_adam_flat": (C.c_int, [_vp, _vp, _vp, _vp, _sz, _f, _f, _f, _f, _i, _vp]),
     "pk_session_create": (C.c_int, [C.POINTER(_vp), _i, _i, _i]),
     "pk_session_destroy": (None, [_vp]),
     "pk_session_load_weights": (C.c_int, [_vp, C.POINTER(pk_mlp)]),

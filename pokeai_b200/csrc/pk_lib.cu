@@ -11,6 +11,7 @@
 #include "pk_common.cuh"
 #include "pk_decide2.cuh"
 #include "pk_update.cuh"
+#include "pk_bn.cuh"
 #include "pk_wide.cuh"
 #include "pk_decide_tc.cuh"
 #include "pk_dense_tc.cuh"
@@ -527,6 +528,7 @@ extern "C" int pk_select(const float* q, const int32_t* mask, int B, int A, cons
 
 // ---- DQN update ---------------------------------------------------------------------------------------
 #include "pk_update_api.inc"
+#include "pk_bn_api.inc"
 
 // pk_dqn_grad without caller scratch and without any allocation: the scratch is pk_static_scratch (above).  No
 // counterpart in the reference; added for callers that cannot allocate.

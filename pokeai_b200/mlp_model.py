@@ -84,7 +84,8 @@ class MLPModel(nn.Module):
         key = (str(device),) + self.weights_key()
         if self._prepared is None or self._prepared_key != key:
             if self.bn and self.training:
-                raise NotImplementedError("train-mode BatchNorm has no kernel; call .eval() (bn is folded)")
+                raise RuntimeError("a bn=True model in training mode has no folded weights: call .eval() for the "
+                                   "inference kernels (forward() in training mode uses batch statistics)")
             self._prepared = ops.prepare_weights(self.folded_state_dict(), device)[0]
             self._prepared_key = key
         return self._prepared
@@ -97,4 +98,7 @@ class MLPModel(nn.Module):
                                "use Agent.act_batch / _calc_q_vector_batch for host arrays")
         if x.requires_grad:
             raise RuntimeError("autograd does not flow through the CUDA forward; the update is Trainer._update")
+        if self.bn and self.training:  # batch statistics, running statistics moved (pk_bn_forward_train)
+            from . import bn_train
+            return bn_train.model_forward_train(self, x)
         return ops.mlp_forward(self.prepared(x.device), self.n_layers, self.n_channels, x.contiguous().float())

@@ -116,9 +116,9 @@ class Trainer:
         self.model_params = model_params.copy()
         self.model_params["input_shape"] = self.feature_extractor.input_shape
         self.model_params["output_dim"] = self.feature_extractor.output_dim
-        if self.model_params.get("bn", False):
-            raise NotImplementedError("train-mode BatchNorm has no kernel (every recorded run of the reference "
-                                      "uses bn=False); inference with a folded eval-mode BN is supported")
+        # bn: true -> train-mode BatchNorm in every forward of the update, as in the reference, whose Trainer never calls
+        # .eval() on model / target_model (trainer.py:41-43): pokeai_b200/bn_train.py, csrc/pk_bn.cuh
+        self._bn = bool(self.model_params.get("bn", False))
         # same construction order as the reference (two random inits, then copy): identical torch RNG use
         self.model, self._flat = self._construct_flat_model()
         self.target_model, self._flat_target = self._construct_flat_model()
@@ -145,8 +145,10 @@ class Trainer:
         self._nl, self._H, self._C = m.n_layers, m.n_channels, m.in_channels
         lib = N.lib()
         from .wide import is_wide
-        self._wide = is_wide(self._H)  # 4 x 2048 and the like: tensor-core path (pokeai_b200/wide.py)
-        if self._wide:
+        self._wide = is_wide(self._H) and not self._bn  # 4 x 2048 and the like: tensor-core path (pokeai_b200/wide.py)
+        if self._bn:  # no folded / prepared copies while training: snapshots fold the running statistics (eval mode)
+            self._prepared = self._prepared_target = None
+        elif self._wide:
             n_prep = lib.pk_wide_prepared_bytes(self._nl, self._H, self._C)
             self._prepared = torch.zeros(n_prep, dtype=torch.uint8, device=self.device)
             self._prepared_target = torch.zeros(n_prep, dtype=torch.uint8, device=self.device)
@@ -157,6 +159,9 @@ class Trainer:
         self._grad = torch.zeros_like(self._flat)
         self._loss = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._staging = None
+        if self._bn:
+            self._bn_ws = {}
+            return
         self._refresh_prepared()
         self._prepared_target.copy_(self._prepared)
 
@@ -170,16 +175,30 @@ class Trainer:
         params = list(model.parameters())
         if flat is None:
             flat = torch.cat([p.detach().reshape(-1) for p in params]).to(self.device, torch.float32)
-        assert flat.numel() == N.lib().pk_mlp_param_floats(model.n_layers, model.n_channels, model.in_channels)
+        if model.bn:
+            assert flat.numel() == N.lib().pk_bn_param_floats(model.n_layers, model.n_channels, model.in_channels)
+        else:
+            assert flat.numel() == N.lib().pk_mlp_param_floats(model.n_layers, model.n_channels, model.in_channels)
         off = 0
         for p in params:
             n = p.numel()
             p.data = flat[off:off + n].view(p.shape)
             p.requires_grad_(False)
             off += n
+        if model.bn:
+            # running_mean / running_var of every layer are views of ONE (n_layers, 2, H) CUDA tensor the kernels move
+            running = torch.stack([torch.stack([b.running_mean, b.running_var]) for b in model.bn_layers]) \
+                .to(self.device, torch.float32).contiguous()
+            for l, b in enumerate(model.bn_layers):
+                b.running_mean = running[l, 0]
+                b.running_var = running[l, 1]
+            model._running = running
         return model, flat
 
     def _refresh_prepared(self) -> None:
+        if self._bn:
+            self.model.mark_updated()
+            return
         if self._wide:
             from . import wide
             wide.prepare_wide(self.model.state_dict(), self.device, out=self._prepared)  # parameters are views of _flat
@@ -189,6 +208,11 @@ class Trainer:
 
     def _snapshot_model(self) -> MLPModel:
         """A frozen copy of the online network (get_train_agent / get_val_agent, trainer.py:123-134)."""
+        if self._bn:  # eval mode: BatchNorm folds into the convs with the running statistics of this moment
+            model = self._construct_model()
+            model.load_state_dict(self._cpu_sd(self.model))
+            model.eval()
+            return model
         model, flat = self._construct_flat_model(self._flat.clone())
         model.eval()
         if not self._wide:  # wide models are prepared by the agent's WideRunner
@@ -231,7 +255,9 @@ class Trainer:
             trainer.total_steps = state["total_steps"]
             trainer.total_battles = state["total_battles"]
             trainer.target_model.load_state_dict(state["target_model"])
-            if trainer._wide:
+            if trainer._bn:
+                pass
+            elif trainer._wide:
                 from . import wide
                 wide.prepare_wide(trainer.target_model.state_dict(), trainer.device, out=trainer._prepared_target)
             else:
@@ -250,7 +276,8 @@ class Trainer:
         self.model.load_state_dict(state_dict)
         self.target_model.load_state_dict(state_dict)
         self._refresh_prepared()
-        self._prepared_target.copy_(self._prepared)
+        if not self._bn:
+            self._prepared_target.copy_(self._prepared)
 
     # -- agents (trainer.py:123-134) ----------------------------------------------------------------------
     def get_train_agent(self):
@@ -314,6 +341,8 @@ class Trainer:
         (sum of this shard's Huber terms / n_global; the all-reduced mean when distributed)."""
         n = len(state)
         n_global = n if n_global is None else n_global
+        if self._bn:
+            return self._update_bn(state, next_state, action, reward, terminal, n_global)
         if self._wide:
             return self._update_wide(state, next_state, action, reward, terminal, n_global)
         self._ensure_staging(max(n, 1))
@@ -489,6 +518,53 @@ class Trainer:
         self._wide_apply()
         return float(self._loss.item())
 
+    def _update_bn(self, state, next_state, action, reward, terminal, n_global: int) -> float:
+        """The update of a bn=True network: every forward in TRAINING mode as in the reference (model(state_batch)
+        trainer.py:163, model / target_model on the non-final next states :157-158,174-175,181-182: batch statistics,
+        running statistics moved, in that order), Huber dq (:184-187), backward through the batch statistics (:192),
+        clamp + Adam (:193-195)."""
+        from . import bn_train, ops
+        if self._dist() is not None:
+            raise NotImplementedError("bn=True under data parallelism needs batch statistics synchronised across ranks; "
+                                      "run the bn=True update on one GPU (the reference is single-process)")
+        n = len(state)
+        if n < 1:
+            raise ValueError("empty minibatch")
+        dev, A = self.device, self.feature_extractor.output_dim
+        nl, H = self._nl, self._H
+        terminal = np.asarray(terminal).astype(bool)
+        idx_nf = np.flatnonzero(~terminal)
+        if len(idx_nf) == 0:
+            raise ValueError("need at least one array to stack")  # np.stack([]) at trainer.py:157
+        slot = np.full(n, -1, dtype=np.int32)
+        slot[idx_nf] = np.arange(len(idx_nf), dtype=np.int32)
+        s_d = ops.packed_to_device(np.ascontiguousarray(state), dev)
+        s2_d = ops.packed_to_device(np.ascontiguousarray(next_state[idx_nf]), dev)
+        a_d = torch.from_numpy(np.ascontiguousarray(action, dtype=np.int32)).to(dev)
+        r_d = torch.from_numpy(np.ascontiguousarray(reward, dtype=np.float32)).to(dev)
+        slot_d = torch.from_numpy(slot).to(dev)
+        feat_s, _ = ops.encode(s_d, A)
+        feat_n, mask_n = ops.encode(s2_d, A)
+        W = self._bn_ws
+        q, W["s"] = bn_train.forward_train(self._flat, self.model._running, nl, H, feat_s, W.get("s"))
+        q_no = None
+        if self.double_dqn:
+            q_no, W["n"] = bn_train.forward_train(self._flat, self.model._running, nl, H, feat_n, W.get("n"))
+        q_nt, W["n"] = bn_train.forward_train(self._flat_target, self.target_model._running, nl, H, feat_n, W.get("n"))
+        dq, loss = bn_train.dqn_dq(q, a_d, r_d, slot_d, q_no, q_nt, mask_n, n_global, self.gamma, self.double_dqn)
+        W["b"] = bn_train.backward(self._flat, nl, H, feat_s, W["s"], dq, self._grad, W.get("b"))
+        opt = self.optimizer
+        opt.step_count += 1
+        bn_train.clamp_adam_flat(self._flat, self._grad, opt.exp_avg, opt.exp_avg_sq, opt.step_count, opt.lr, opt.betas,
+                                 opt.eps)
+        for b in self.model.bn_layers:
+            b.num_batches_tracked += 2 if self.double_dqn else 1
+        for b in self.target_model.bn_layers:
+            b.num_batches_tracked += 1
+        self.model.mark_updated()
+        self.target_model.mark_updated()
+        return float(loss.item())
+
     def _update(self):
         idx = self.replay_buffer.sample_indices(self.batch_size)
         state, next_state, action, reward, terminal = self.replay_buffer.gather(idx)
@@ -506,5 +582,11 @@ class Trainer:
 
     def _target_update(self):  # trainer.py:197-198
         self._flat_target.copy_(self._flat)
+        if self._bn:  # load_state_dict copies the buffers too: running statistics and num_batches_tracked
+            self.target_model._running.copy_(self.model._running)
+            for bt, bm in zip(self.target_model.bn_layers, self.model.bn_layers):
+                bt.num_batches_tracked.copy_(bm.num_batches_tracked)
+            self.target_model.mark_updated()
+            return
         self._prepared_target.copy_(self._prepared)
         self.target_model.mark_updated(None if self._wide else self._prepared_target)

@@ -36,6 +36,22 @@ def test_layout_sizes():
     assert lib.pk_mlp_prepared_floats(0, 64, 617) == 0
 
 
+def test_bn_layout_matches_the_module():
+    """pk_bn_param_floats == the parameter count of MLPModel(bn=True) (conv layers without bias + BatchNorm affine +
+    head), workspace sizes grow with the batch, and bad shapes give 0."""
+    from pokeai_b200 import _native as N
+    from pokeai_b200.mlp_model import MLPModel
+    lib = N.lib()
+    for nl, H in ((2, 64), (3, 24), (1, 100)):
+        m = MLPModel((617, 9), 9, n_layers=nl, n_channels=H, bn=True)
+        assert lib.pk_bn_param_floats(nl, H, 617) == sum(p.numel() for p in m.parameters())
+        assert [k for k, _ in m.named_parameters()][:nl] == [f"layers.{i}.weight" for i in range(nl)]
+    assert lib.pk_bn_param_floats(0, 64, 617) == 0 and lib.pk_bn_param_floats(9, 64, 617) == 0
+    small, big = lib.pk_bn_workspace_floats(2, 64, 32, 9), lib.pk_bn_workspace_floats(2, 64, 64, 9)
+    assert big - small == 2 * 2 * 32 * 9 * 64  # pre-norm and post-ReLU activations of every layer
+    assert lib.pk_bn_backward_scratch_floats(2, 64, 64, 9) - lib.pk_bn_backward_scratch_floats(2, 64, 32, 9) == 2 * 32 * 9 * 64
+
+
 def test_calls_fail_loudly_without_init_or_device():
     import torch
     from pokeai_b200 import _native as N
