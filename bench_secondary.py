@@ -326,6 +326,33 @@ def leg_update(ctx, NG=32768, nl=2, H=64, steps=20):
     return out
 
 
+# ---- the same update with bn: true (train-mode BatchNorm, csrc/pk_bn.cuh): single GPU, plain FP32 kernels ----------
+def leg_bn_update(ctx, NG=4096, nl=2, H=64, steps=10):
+    """Trainer._update_from_arrays of a bn=True network through the public host API (host arrays in, loss out, so every
+    step includes its host->device copies): a reported figure for a path built for coverage, not tuned."""
+    if ctx.world > 1:
+        return None  # batch statistics are not synchronised across ranks: Trainer refuses a data-parallel bn update
+    import numpy as np
+    import torch
+    from pokeai_b200.trainer import Trainer
+    torch.manual_seed(11)
+    tr = Trainer({"n_layers": nl, "n_channels": H, "bn": True}, {"batch_size": NG, "lr": 1e-4},
+                 {"party_size": PARTY_SIZE}, device=ctx.dev)
+    sets = [synth_transitions(NG, 40 + i) for i in range(2)]
+    losses = []
+
+    def step(i):
+        s, s2, ac, r, t = sets[i % 2]
+        losses.append(tr._update_from_arrays(s, s2, ac, r, t))
+
+    ms = _timed(ctx, step, steps)
+    return {"config": f"DQN update with bn: true (train-mode BatchNorm in all three forwards, mlp_model.py:12-15): {NG} "
+                      f"transitions, MLP {nl}x{H}, Double DQN, through Trainer._update_from_arrays (host arrays in, loss out)",
+            "transitions_per_s": NG / (ms * 1e-3), "update_ms": ms, "steps": steps, "scaling": "single GPU only",
+            "loss_finite": bool(np.all(np.isfinite(losses))),
+            "parity": "tests/test_gpu_bn.py: golden vectors of the reference Trainer._update with bn: true; torch fp64"}
+
+
 def sd_numel(sd):
     return int(sum(v.numel() for v in sd.values()))
 
@@ -600,7 +627,7 @@ def _c_packer_in_use():
 
 
 def run_all(ctx, skip=()):
-    legs = [("shard65536", leg_shard65536), ("dense", leg_dense_forward), ("update", leg_update), ("wide", leg_wide), ("wide_update", leg_wide_update),
+    legs = [("shard65536", leg_shard65536), ("dense", leg_dense_forward), ("update", leg_update), ("bn_update", leg_bn_update), ("wide", leg_wide), ("wide_update", leg_wide_update),
             ("gpu_reference", leg_gpu_reference), ("concurrent64", leg_concurrent64)]
     import torch
     out = []

@@ -321,6 +321,13 @@ PK_API size_t pk_bn_workspace_floats(int n_layers, int n_channels, int B, int A)
 PK_API size_t pk_bn_backward_scratch_floats(int n_layers, int n_channels, int B, int A);
 PK_API int pk_bn_forward_train(const float* params, float* running, int n_layers, int n_channels, int in_channels,
                         const float* feat, int B, int A, float* ws, float* q, void* stream);
+/* The same forward straight from PACKED records (what Trainer._update_bn uses): layer 0 is gathered -- a feature column
+ * is the battle's 50 state values plus at most eight one-hot rows (state_feature_extractor.py:92-197,
+ * choice_to_vec.py:40-61), so 58 rows of W0^T are touched instead of 617 and no dense feature block exists.  in_channels
+ * must equal pk_n_channels().  ws: pk_bn_packed_workspace_floats(...) floats.  mask (B, A) int32 may be NULL. */
+PK_API size_t pk_bn_packed_workspace_floats(int n_layers, int n_channels, int in_channels, int B, int A);
+PK_API int pk_bn_forward_train_packed(const float* params, float* running, int n_layers, int n_channels, int in_channels,
+                               const pk_obs* packed, int B, int A, float* ws, float* q, int32_t* mask, void* stream);
 /* Double-DQN target, smooth-L1 loss (mean over n_global) and d loss / d q (trainer.py:163-187).  slot[i] = row of
  * transition i's next state in the COMPACTED non-final arrays q_next_online / q_next_target / mask_next (the reference
  * forwards only the non-final next states, trainer.py:157-158), -1 when terminal.  dq: (n, A), zero except at action[i].
@@ -332,6 +339,13 @@ PK_API int pk_bn_dqn_dq(const float* q, const int32_t* action, const float* rewa
  * in `params` order (not clamped).  scratch: pk_bn_backward_scratch_floats(...) floats, 16-byte aligned. */
 PK_API int pk_bn_backward(const float* params, int n_layers, int n_channels, int in_channels, const float* feat, int B,
                    int A, const float* ws, const float* dq, float* scratch, float* grad, void* stream);
+/* pk_bn_backward after pk_bn_forward_train_packed on the same records: the one-hot rows of dW0 are accumulated with
+ * coalesced float atomics (their order, hence the last bit, varies from run to run), the 50 state rows by one small GEMM
+ * over the batch; weights of features that never occur get a gradient of exactly 0.  scratch:
+ * pk_bn_packed_backward_scratch_floats(...) floats. */
+PK_API size_t pk_bn_packed_backward_scratch_floats(int n_layers, int n_channels, int in_channels, int B, int A);
+PK_API int pk_bn_backward_packed(const float* params, int n_layers, int n_channels, int in_channels, const pk_obs* packed,
+                          int B, int A, const float* ws, const float* dq, float* scratch, float* grad, void* stream);
 /* pk_clamp_adam over a plain vector of n floats (no prepared copies): clamp to [-1, 1], Adam (trainer.py:193-195). */
 PK_API int pk_clamp_adam_flat(float* params, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
                        float beta1, float beta2, float eps, int step, void* stream);

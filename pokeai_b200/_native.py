@@ -96,6 +96,10 @@ _SIGNATURES = {
     "pk_bn_forward_train": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "pk_bn_dqn_dq": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _vp]),
     "pk_bn_backward": (C.c_int, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "pk_bn_packed_workspace_floats": (_sz, [_i, _i, _i, _i, _i]),
+    "pk_bn_forward_train_packed": (C.c_int, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "pk_bn_packed_backward_scratch_floats": (_sz, [_i, _i, _i, _i, _i]),
+    "pk_bn_backward_packed": (C.c_int, [_vp, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "pk_clamp_adam_flat": (C.c_int, [_vp, _vp, _vp, _vp, _sz, _f, _f, _f, _f, _i, _vp]),
     "pk_session_create": (C.c_int, [C.POINTER(_vp), _i, _i, _i]),
     "pk_session_destroy": (None, [_vp]),

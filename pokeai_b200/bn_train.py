@@ -60,6 +60,42 @@ def forward_train(flat: torch.Tensor, running: Optional[torch.Tensor], n_layers:
     return q, ws
 
 
+def forward_train_packed(flat: torch.Tensor, running: Optional[torch.Tensor], n_layers: int, H: int, packed: torch.Tensor,
+                         A: int, ws: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """packed (B, 144) u8 CUDA records -> (q (B, A), mask (B, A) int32, ws): the same forward with layer 0 gathered from
+    the records (no dense feature block)."""
+    from .ops import _check_packed, n_channels
+    B = _check_packed(packed)
+    dev, C = packed.device, n_channels()
+    assert flat.is_cuda and flat.is_contiguous() and flat.numel() == param_floats(n_layers, H, C)
+    if running is not None:
+        assert running.is_cuda and running.is_contiguous() and running.shape == (n_layers, 2, H)
+    need = int(N.lib().pk_bn_packed_workspace_floats(n_layers, H, C, B, A))
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, dtype=torch.float32, device=dev)
+    q = torch.empty((B, A), dtype=torch.float32, device=dev)
+    mask = torch.empty((B, A), dtype=torch.int32, device=dev)
+    N.check(N.lib().pk_bn_forward_train_packed(flat.data_ptr(), running.data_ptr() if running is not None else None,
+                                               n_layers, H, C, packed.data_ptr(), B, A, ws.data_ptr(), q.data_ptr(),
+                                               mask.data_ptr(), _stream(dev)))
+    return q, mask, ws
+
+
+def backward_packed(flat: torch.Tensor, n_layers: int, H: int, packed: torch.Tensor, A: int, ws: torch.Tensor,
+                    dq: torch.Tensor, grad: torch.Tensor, scratch: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """backward() for a forward that ran on packed records (forward_train_packed with the same `packed` and `ws`)."""
+    from .ops import _check_packed, n_channels
+    B = _check_packed(packed)
+    dev, C = packed.device, n_channels()
+    need = int(N.lib().pk_bn_packed_backward_scratch_floats(n_layers, H, C, B, A))
+    if scratch is None or scratch.numel() < need:
+        scratch = torch.empty(need, dtype=torch.float32, device=dev)
+    assert grad.is_cuda and grad.is_contiguous() and grad.numel() == flat.numel() and dq.is_contiguous()
+    N.check(N.lib().pk_bn_backward_packed(flat.data_ptr(), n_layers, H, C, packed.data_ptr(), B, A, ws.data_ptr(),
+                                          dq.data_ptr(), scratch.data_ptr(), grad.data_ptr(), _stream(dev)))
+    return scratch
+
+
 def dqn_dq(q: torch.Tensor, action: torch.Tensor, reward: torch.Tensor, slot: torch.Tensor,
            q_next_online: Optional[torch.Tensor], q_next_target: torch.Tensor, mask_next: torch.Tensor, n_global: int,
            gamma: float, double_dqn: bool) -> Tuple[torch.Tensor, torch.Tensor]:

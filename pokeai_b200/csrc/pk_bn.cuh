@@ -15,6 +15,8 @@
 //   pk_clamp_adam_flat_kernel   clamp + Adam over a plain vector (same arithmetic as pk_clamp_adam_kernel)
 #pragma once
 #include "pk_common.cuh"
+#include "pk_decide.cuh"  // pk_state_feature, pk_choice_row
+#include "pk_update.cuh"  // PkAdam
 
 // flat parameter order of a bn=True MLPModel (nn.Module.parameters(): layers.*.weight, then bn_layers.*.weight / .bias
 // interleaved per layer, then output.weight, output.bias); conv layers carry no bias (mlp_model.py:12)
@@ -337,4 +339,99 @@ __global__ void pk_clamp_adam_flat_kernel(float* __restrict__ params, const floa
   params[i] = params[i] + (-h.step_size * mi) / denom;
   m[i] = mi;
   v[i] = vi;
+}
+
+// ---- layer 0 from the PACKED records ---------------------------------------------------------------------------------
+// A feature column is the battle's 50 state values (shared by its action columns, state_feature_extractor.py:92-197) plus at
+// most eight one-hot choice rows (choice_to_vec.py:40-61): z0 = sum_k sv[k] W0[:, k] + sum_t W0[:, row_t], 58 rows of
+// W0^T instead of 617, and no dense (B, 617, A) block in HBM.  One warp per battle, lanes over output channels.
+#define PK_BN_L0_WARPS 8
+struct PkBnL0Smem {
+  uint4 rec[PK_BN_L0_WARPS][9];
+  float sv[PK_BN_L0_WARPS][64];
+  int idx[PK_BN_L0_WARPS][8 * PK_MAX_ACTIONS];
+};
+// parses battle b into this warp's slots; returns n_act (choice rows of columns >= n_act are -1: feature_extractor.py:49)
+__device__ __forceinline__ int pk_bn_l0_parse(PkBnL0Smem& sm, int warp, int lane, const uint4* __restrict__ packed, int b,
+                                              int A) {
+  if (lane < 9) sm.rec[warp][lane] = __ldg(packed + (size_t)b * 9 + lane);
+  __syncwarp();
+  const uint8_t* r = reinterpret_cast<const uint8_t*>(sm.rec[warp]);
+  const int na = min((int)r[PK_OFF_NACT], A);
+  sm.sv[warp][lane] = pk_state_feature(r, lane);
+  sm.sv[warp][lane + 32] = pk_state_feature(r, lane + 32);
+  for (int e = lane; e < 8 * A; e += 32) {
+    const int c = e >> 3;
+    sm.idx[warp][e] = c < na ? pk_choice_row(r, c, e & 7) : -1;
+  }
+  __syncwarp();
+  return na;
+}
+
+// in [R][Cc] -> out [Cc][R] (out[c * R + r] = in[r * Cc + c]) for the rows r >= r_from of `in`; block (32, 8)
+__global__ void pk_bn_transpose_kernel(const float* __restrict__ in, int R, int Cc, int r_from, float* __restrict__ out) {
+  __shared__ float t[32][33];
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    t[i][threadIdx.x] = (r < R && c < Cc) ? in[(size_t)r * Cc + c] : 0.0f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < R && c < Cc && r >= r_from) out[(size_t)c * R + r] = t[threadIdx.x][i];
+  }
+}
+
+__global__ void __launch_bounds__(32 * PK_BN_L0_WARPS)
+pk_bn_l0_fwd_kernel(const uint4* __restrict__ packed, int B, int A, const float* __restrict__ w0t, int H,
+                    float* __restrict__ z, int* __restrict__ mask) {
+  __shared__ PkBnL0Smem sm;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * PK_BN_L0_WARPS + warp;
+  if (b >= B) return;
+  const int na = pk_bn_l0_parse(sm, warp, lane, packed, b, A);
+  if (mask != nullptr && lane < A) mask[(size_t)b * A + lane] = lane < na ? 1 : 0;
+  for (int o = lane; o < H; o += 32) {
+    float base = 0.0f;
+#pragma unroll 10
+    for (int k = 0; k < PK_N_STATE; ++k) base = fmaf(sm.sv[warp][k], w0t[(size_t)k * H + o], base);
+    for (int a = 0; a < A; ++a) {
+      float v = base;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int row = sm.idx[warp][8 * a + t];
+        if (row >= 0) v += w0t[(size_t)row * H + o];
+      }
+      z[((size_t)b * A + a) * H + o] = v;
+    }
+  }
+}
+
+// backward of layer 0: the one-hot part of dW0 as coalesced atomics into a TRANSPOSED buffer gw0t [C][H] (zeroed by the
+// caller); the state part leaves as two compact matrices, SV [B][64] and DS [B][H] = sum over the battle's columns of
+// dz, which one small GEMM (pk_bn_gemm_kernel) contracts over the batch
+__global__ void __launch_bounds__(32 * PK_BN_L0_WARPS)
+pk_bn_l0_bwd_kernel(const uint4* __restrict__ packed, int B, int A, const float* __restrict__ dz, int H,
+                    float* __restrict__ gw0t, float* __restrict__ svm, float* __restrict__ dsm) {
+  __shared__ PkBnL0Smem sm;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * PK_BN_L0_WARPS + warp;
+  if (b >= B) return;
+  pk_bn_l0_parse(sm, warp, lane, packed, b, A);
+  svm[(size_t)b * 64 + lane] = sm.sv[warp][lane];
+  svm[(size_t)b * 64 + lane + 32] = sm.sv[warp][lane + 32];
+  for (int o = lane; o < H; o += 32) {
+    float ds = 0.0f;
+    for (int a = 0; a < A; ++a) {
+      const float d = dz[((size_t)b * A + a) * H + o];
+      ds += d;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int row = sm.idx[warp][8 * a + t];
+        if (row >= 0) atomicAdd(gw0t + (size_t)row * H + o, d);
+      }
+    }
+    dsm[(size_t)b * H + o] = ds;
+  }
 }

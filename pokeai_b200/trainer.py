@@ -543,16 +543,15 @@ class Trainer:
         a_d = torch.from_numpy(np.ascontiguousarray(action, dtype=np.int32)).to(dev)
         r_d = torch.from_numpy(np.ascontiguousarray(reward, dtype=np.float32)).to(dev)
         slot_d = torch.from_numpy(slot).to(dev)
-        feat_s, _ = ops.encode(s_d, A)
-        feat_n, mask_n = ops.encode(s2_d, A)
         W = self._bn_ws
-        q, W["s"] = bn_train.forward_train(self._flat, self.model._running, nl, H, feat_s, W.get("s"))
+        fwd = bn_train.forward_train_packed  # layer 0 gathered from the records: no dense (B, 617, A) block
+        q, _, W["s"] = fwd(self._flat, self.model._running, nl, H, s_d, A, W.get("s"))
         q_no = None
         if self.double_dqn:
-            q_no, W["n"] = bn_train.forward_train(self._flat, self.model._running, nl, H, feat_n, W.get("n"))
-        q_nt, W["n"] = bn_train.forward_train(self._flat_target, self.target_model._running, nl, H, feat_n, W.get("n"))
+            q_no, _, W["n"] = fwd(self._flat, self.model._running, nl, H, s2_d, A, W.get("n"))
+        q_nt, mask_n, W["n"] = fwd(self._flat_target, self.target_model._running, nl, H, s2_d, A, W.get("n"))
         dq, loss = bn_train.dqn_dq(q, a_d, r_d, slot_d, q_no, q_nt, mask_n, n_global, self.gamma, self.double_dqn)
-        W["b"] = bn_train.backward(self._flat, nl, H, feat_s, W["s"], dq, self._grad, W.get("b"))
+        W["b"] = bn_train.backward_packed(self._flat, nl, H, s_d, A, W["s"], dq, self._grad, W.get("b"))
         opt = self.optimizer
         opt.step_count += 1
         bn_train.clamp_adam_flat(self._flat, self._grad, opt.exp_avg, opt.exp_avg_sq, opt.step_count, opt.lr, opt.betas,

@@ -115,7 +115,8 @@ def test_bn_forward_and_backward_match_torch(tables, nl, H, B, ps, seed):
             b.running_var.uniform_(0.5, 1.5)
     ref = copy.deepcopy(model).double()
     dev = torch.device(DEV)
-    feat, _ = ops.encode(ops.packed_to_device(synth_packed(B, seed=3, party_size=ps, kind="ragged", tables=tables), dev), A)
+    packed = ops.packed_to_device(synth_packed(B, seed=3, party_size=ps, kind="ragged", tables=tables), dev)
+    feat, mask = ops.encode(packed, A)
     x = feat.cpu().double()
     for p_ in ref.parameters():
         p_.requires_grad_(True)
@@ -150,6 +151,16 @@ def test_bn_forward_and_backward_match_torch(tables, nl, H, B, ps, seed):
     bn_train.backward(flat, nl, H, feat, ws, dq.to(dev).contiguous(), grad)
     gs = float(want.abs().max())
     assert float((grad.cpu().double() - want).abs().max()) <= 5e-6 * gs
+    # the same straight from the packed records (what Trainer uses): layer 0 gathered, dW0's one-hot rows by atomics
+    qp, maskp, wsp = bn_train.forward_train_packed(flat, None, nl, H, packed, A)
+    assert torch.equal(maskp, mask)
+    assert float((qp.cpu().double() - q_ref.detach()).abs().max()) <= 5e-6 * scale
+    gradp = torch.full_like(flat, float("nan"))
+    bn_train.backward_packed(flat, nl, H, packed, A, wsp, dq.to(dev).contiguous(), gradp)
+    assert float((gradp.cpu().double() - want).abs().max()) <= 5e-6 * gs
+    unused = (feat.abs().amax(dim=(0, 2)) == 0).cpu()  # feature rows that never occur in this batch
+    gw0 = gradp[:H * tables.n_channels].view(H, tables.n_channels).cpu()
+    assert int(unused.sum()) > 0 and bool((gw0[:, unused] == 0).all())  # exactly zero: Adam leaves those weights alone
     # in eval mode the same module folds BatchNorm (running statistics) and runs the inference kernel
     model.eval()
     ref.eval()
