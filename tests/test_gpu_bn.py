@@ -160,7 +160,8 @@ def test_bn_forward_and_backward_match_torch(tables, nl, H, B, ps, seed):
     assert float((gradp.cpu().double() - want).abs().max()) <= 5e-6 * gs
     unused = (feat.abs().amax(dim=(0, 2)) == 0).cpu()  # feature rows that never occur in this batch
     gw0 = gradp[:H * tables.n_channels].view(H, tables.n_channels).cpu()
-    assert int(unused.sum()) > 0 and bool((gw0[:, unused] == 0).all())  # exactly zero: Adam leaves those weights alone
+    assert bool((gw0[:, unused] == 0).all())  # exactly zero: Adam leaves those weights alone
+    assert B > 100 or int(unused.sum()) > 100  # the small batch leaves most of the 617 rows unused
     # in eval mode the same module folds BatchNorm (running statistics) and runs the inference kernel
     model.eval()
     ref.eval()
