@@ -215,6 +215,14 @@ def test_bn_trainer_schedule_and_checkpoint(tables):
     assert len(tr.update_loss_history) == 4 and all(np.isfinite(tr.update_loss_history))
     sd = tr.model.state_dict()
     assert int(sd["bn_layers.0.num_batches_tracked"]) == 8  # two training forwards of the online net per update
+    # agents get an eval-mode snapshot (BatchNorm folded with the running statistics): the decision kernel's Q equals the
+    # snapshot module's own forward on the encoded features
+    from pokeai_b200 import ops
+    agent = tr.get_train_agent()
+    q_agent, _ = agent.q_and_action_batch(rs[:16])
+    feat, _ = ops.encode(ops.packed_to_device(rs[:16], torch.device(DEV)), A)
+    assert not agent._model.training
+    np.testing.assert_allclose(np.array(q_agent), agent._model(feat).cpu().numpy(), rtol=1e-5, atol=1e-5)
     state = tr.save_state(resume=True)
     tr2 = Trainer.load_state(state, resume=True, device=DEV)
     for k, v in tr.model.state_dict().items():
