@@ -68,6 +68,10 @@
 #define PKD_WARPS (PKD_TW + 2 + PKD_XPW)
 #define PKD_KBF 64                  // feature rows per k-block: a TMA bulk load costs ~75 cycles of the SM's TMA unit
                                     // whatever its size (tools/micro/bulk_load_bw.cu), so pieces must be >= 2 KB
+#define PKD_XK 1                    // MMA k-blocks per X stage.  2 (one 4.6 KB bulk load per battle and 128 feature rows: half the
+                                    // loads for the TMA unit, but only two X stages fit) passes parity and is SLOWER: 396 against
+                                    // 381-385 us at 65 536 states -- the X side is not bound by the number of loads
+#define PKD_XKF (PKD_KBF * PKD_XK)
 #define PKD_A_STAGES 2
 #define PKD_W_TILE 16384u           // [W0 hi ; W0 lo] of 32 input rows: 128 rows x 128 B (one PkLayout::tc0 tile)
 #define PKD_W_STAGE 32768u          // one k-block: two tiles
@@ -110,7 +114,7 @@ __host__ __device__ inline PkdSmemPlan pkd_smem_plan(const PkLayout& lay, int A,
   o += 8u * (2u * PKD_X_STAGES_MAX + 2u * PKD_A_STAGES + 2u * PKD_W_STAGES + 4u) + 16u;
   o = (o + 127u) & ~127u;
   p.x = o;
-  p.piece = 4u * PKD_KBF * (unsigned)A + 32u;  // the aligned cover of a k-block's bytes at any 4-byte alignment
+  p.piece = 4u * PKD_XKF * (unsigned)A + 32u;  // the aligned cover of an X block's bytes at any 4-byte alignment
   p.x_stage = (nb * p.piece + 127u) & ~127u;
   const unsigned room = max_smem > o + 1024u ? max_smem - o - 1024u : 0u;
   p.x_stages = room / p.x_stage;
@@ -189,6 +193,7 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
   const int nb = pkd_battles_per_tile(A), rows = nb * A;
   const int L = lay.C * A;
   const int NKB = (lay.C + PKD_KBF - 1) / PKD_KBF;
+  const int NXB = (NKB + PKD_XK - 1) / PKD_XK;  // X blocks per tile
   const int ntiles = (B + nb - 1) / nb;
   const int n_hidden = lay.n_layers - 1;  // >= 1
   const int npairs = (ntiles + 1) >> 1;
@@ -285,8 +290,8 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
     uint32_t xit = 0;
     unsigned long long* ptr = (blockIdx.x == 0 && lane == 0 && warp == PKD_XPRODUCER) ? trace : nullptr;
     for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
-      for (int kt = 0; kt < 2 * NKB; ++kt, ++xit) {
-        const int kb = kt >> 1, tile = 2 * pair + (kt & 1);
+      for (int kt = 0; kt < 2 * NXB; ++kt, ++xit) {
+        const int kb = kt >> 1, tile = 2 * pair + (kt & 1);  // kb: the X block
         const long long b = (long long)tile * nb + pb;
         const bool mine = pb < nb && tile < ntiles && b < B;
         const int xs = (int)(xit % (uint32_t)XS);
@@ -298,9 +303,9 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
         unsigned char* dst = smem + plan.x + (unsigned)xs * plan.x_stage + (unsigned)pb * plan.piece;
         if (mine) {
           const unsigned long long addr =
-              feat_addr + 4ull * ((unsigned long long)b * L + (unsigned long long)kb * PKD_KBF * A);
+              feat_addr + 4ull * ((unsigned long long)b * L + (unsigned long long)kb * PKD_XKF * A);
           const uint32_t mis = (uint32_t)(addr & 15ull);
-          const uint32_t len = (uint32_t)min(PKD_KBF, lay.C - kb * PKD_KBF) * (uint32_t)A * 4u;
+          const uint32_t len = (uint32_t)min(PKD_XKF, lay.C - kb * PKD_XKF) * (uint32_t)A * 4u;
           src = addr - mis;
           bytes = (mis + len + 15u) & ~15u;
           if (src + bytes > arr_end16) {
@@ -405,26 +410,31 @@ pk_dense_tc_kernel(const float* __restrict__ feat, int B, int A, const float* __
     bool first = true;
     unsigned long long* ttr = (blockIdx.x == 0 && threadIdx.x == 0) ? trace : nullptr;
     uint32_t sit = 0;  // this set's iteration count: (pair, k-block)
+    uint32_t xsit = 0;  // X blocks this set has consumed
     bool lo_clean[2] = {false, false};  // this warp's two lo groups of its A stage hold zeros
     for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
       const int tile0 = 2 * pair;
       const uint32_t mis = (uint32_t)(
           (feat_addr + 4ull * (unsigned long long)((long long)(tile0 + tset) * nb + rbi) * (unsigned long long)L) & 15ull);
       for (int kb = 0; kb < NKB; ++kb, ++sit) {
-        const uint32_t xit = 2u * sit + (uint32_t)tset;  // X stages alternate between the pair's tiles
+        const uint32_t xit = 2u * xsit + (uint32_t)tset;  // X stages alternate between the pair's tiles
         const int xs = (int)(xit % (uint32_t)XS);
+        const int sub = kb % PKD_XK;  // which 64 rows of the X block
         const uint32_t aph = sit & 1u;
         pkd_trace(ttr, 0, sit, 0);
-        pk_mbar_wait(x_full + xs, (xit / (uint32_t)XS) & 1u);
+        if (sub == 0) pk_mbar_wait(x_full + xs, (xit / (uint32_t)XS) & 1u);
         pkd_trace(ttr, 0, sit, 1);
-        const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_row + mis;
+        const uint32_t xb = x_u32 + (uint32_t)xs * plan.x_stage + src_row + mis + (uint32_t)(sub * PKD_KBF * A) * 4u;
         const int k0 = kb * PKD_KBF + (PKD_KBF / 2) * khalf;
         float x[PKD_KBF / 2];
 #pragma unroll
         for (int j = 0; j < PKD_KBF / 2; ++j) x[j] = (row_ok && k0 + j < lay.C) ? pkd_lds(xb + (uint32_t)(j * A) * 4u) : 0.0f;
         pkd_trace(ttr, 0, sit, 2);
         __syncwarp();
-        if (lane == 0) pkw_mbar_arrive(x_empty + xs);
+        if (sub == PKD_XK - 1 || kb == NKB - 1) {  // the block's last rows are in registers: the stage may be refilled
+          if (lane == 0) pkw_mbar_arrive(x_empty + xs);
+          ++xsit;
+        }
         pk_mbar_wait(a_empty + tset, aph ^ 1u);
         pkw_tc_fence_after();
         pkd_trace(ttr, 0, sit, 3);

@@ -1,9 +1,4 @@
 #!/bin/bash
 set -u
-OUT=gpurun_out
-mkdir -p $OUT
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > $OUT/gpu_r02.txt 2>&1
-echo "== pytest"; timeout 900 python -m pytest tests -m gpu -x -q -s > $OUT/pytest_r02.log 2>&1; echo "pytest rc=$?"; tail -2 $OUT/pytest_r02.log
-echo "== smoke"; timeout 300 python __graft_entry__.py --smoke > $OUT/smoke_r02.log 2>&1; echo "smoke rc=$?"; tail -1 $OUT/smoke_r02.log
-echo "== bench"; timeout 900 python bench.py --steps 20 --warmup 5 > $OUT/bench_r02.json 2> $OUT/bench_r02.err; echo "bench rc=$?"; cut -c1-200 $OUT/bench_r02.json
-echo "== bench reference"; timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > $OUT/bench_ref_r02.json 2> $OUT/bench_ref_r02.err; echo "rc=$?"; cut -c1-300 $OUT/bench_ref_r02.json
+echo "== pytest dense tc"; timeout 200 python -m pytest tests/test_gpu_decide.py tests/test_gpu_agents.py -m gpu -x -q -k "dense" 2>&1 | tail -5
+for B in 4096 65536; do B=$B timeout 120 python tools/quick_time.py 2>&1 | grep "^dense"; done
