@@ -66,6 +66,7 @@ struct PkBnOp {
   int rdiv, kdiv, k_fast;
 };
 __device__ __forceinline__ float pk_bn_op_at(const PkBnOp& o, int r, int k) {
+  if (o.rdiv == 1 && o.kdiv == 1) return o.p[(long long)r * o.r_hi + (long long)k * o.k_hi];  // plain strided matrix
   return o.p[(long long)(r / o.rdiv) * o.r_hi + (long long)(r % o.rdiv) * o.r_lo + (long long)(k / o.kdiv) * o.k_hi +
              (long long)(k % o.kdiv) * o.k_lo];
 }

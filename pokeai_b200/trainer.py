@@ -538,11 +538,26 @@ class Trainer:
             raise ValueError("need at least one array to stack")  # np.stack([]) at trainer.py:157
         slot = np.full(n, -1, dtype=np.int32)
         slot[idx_nf] = np.arange(len(idx_nf), dtype=np.int32)
-        s_d = ops.packed_to_device(np.ascontiguousarray(state), dev)
-        s2_d = ops.packed_to_device(np.ascontiguousarray(next_state[idx_nf]), dev)
-        a_d = torch.from_numpy(np.ascontiguousarray(action, dtype=np.int32)).to(dev)
-        r_d = torch.from_numpy(np.ascontiguousarray(reward, dtype=np.float32)).to(dev)
-        slot_d = torch.from_numpy(slot).to(dev)
+        # one pinned block, one asynchronous copy: [state n*144 | non-final next m*144 | action | reward | slot]
+        m = len(idx_nf)
+        off_n, off_a = n * PK_OBS_BYTES, (n + m) * PK_OBS_BYTES
+        off_r, off_s, total = off_a + 4 * n, off_a + 8 * n, off_a + 12 * n
+        st = self._bn_ws.get("stage")
+        if st is None or st[0].numel() < total:
+            cap = 2 * total
+            st = self._bn_ws["stage"] = (torch.empty(cap, dtype=torch.uint8, pin_memory=True),
+                                         torch.empty(cap, dtype=torch.uint8, device=dev))
+        host, dblk = st
+        hn = host.numpy()
+        hn[:off_n] = np.ascontiguousarray(state).view(np.uint8).reshape(-1)
+        hn[off_n:off_a] = np.ascontiguousarray(next_state[idx_nf]).view(np.uint8).reshape(-1)
+        hn[off_a:off_r].view(np.int32)[:] = action
+        hn[off_r:off_s].view(np.float32)[:] = reward
+        hn[off_s:total].view(np.int32)[:] = slot
+        dblk[:total].copy_(host[:total], non_blocking=True)
+        s_d, s2_d = dblk[:off_n].view(n, PK_OBS_BYTES), dblk[off_n:off_a].view(m, PK_OBS_BYTES)
+        a_d, r_d = dblk[off_a:off_r].view(torch.int32), dblk[off_r:off_s].view(torch.float32)
+        slot_d = dblk[off_s:total].view(torch.int32)
         W = self._bn_ws
         fwd = bn_train.forward_train_packed  # layer 0 gathered from the records: no dense (B, 617, A) block
         q, _, W["s"] = fwd(self._flat, self.model._running, nl, H, s_d, A, W.get("s"))
