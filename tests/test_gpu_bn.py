@@ -235,3 +235,68 @@ def test_bn_trainer_schedule_and_checkpoint(tables):
     random.setstate(st)
     tr2._update()
     assert tr.update_loss_history[-1] == pytest.approx(tr2.update_loss_history[-1], abs=1e-7)
+
+
+@pytest.mark.parametrize("n,term,double", [(1, [0], True), (2, [1, 0], True), (3, [0, 1, 0], False), (5, [0, 0, 0, 0, 1], True)])
+def test_bn_update_tiny_batches_match_torch(tables, n, term, double):
+    """The whole update at batch sizes below every tile size (one transition = six columns for the statistics; a single
+    non-final next state) against the update of trainer.py:152-195 written out with torch autograd in float64."""
+    import copy
+    from pokeai_b200 import ops
+    from pokeai_b200.mlp_model import MLPModel
+    from pokeai_b200.packed import synth_packed
+    from pokeai_b200.trainer import Trainer
+    ps, A, nl, H, gamma = 3, 6, 2, 16, 0.9
+    torch.manual_seed(40 + n)
+    tr = Trainer({"n_layers": nl, "n_channels": H, "bn": True}, {"batch_size": n, "gamma": gamma, "double_dqn": double},
+                 {"party_size": ps}, device=DEV)
+    proto = MLPModel((tables.n_channels, A), A, n_layers=nl, n_channels=H, bn=True)
+    tproto = MLPModel((tables.n_channels, A), A, n_layers=nl, n_channels=H, bn=True)
+    with torch.no_grad():
+        for m_ in (proto, tproto):
+            for b in m_.bn_layers:
+                b.weight.uniform_(0.5, 1.5)
+                b.bias.normal_(0, 0.1)
+                b.running_mean.normal_(0, 0.2)
+                b.running_var.uniform_(0.5, 1.5)
+    tr.model.load_state_dict(proto.state_dict())
+    tr.target_model.load_state_dict(tproto.state_dict())
+    ref, tgt = copy.deepcopy(proto).double(), copy.deepcopy(tproto).double()
+    for p_ in ref.parameters():
+        p_.requires_grad_(True)
+    rs = synth_packed(n, seed=70 + n, party_size=ps, kind="ragged", tables=tables)
+    rn = synth_packed(n, seed=80 + n, party_size=ps, kind="ragged", tables=tables)
+    rng = np.random.default_rng(n)
+    action = (rng.random(n) * rs["n_act"]).astype(np.int64)
+    reward = rng.uniform(-2, 2, n).astype(np.float32)
+    terminal = np.array(term, dtype=bool)
+    dev = torch.device(DEV)
+    fs = ops.encode(ops.packed_to_device(rs, dev), A)[0].cpu().double()
+    fn, mn = ops.encode(ops.packed_to_device(rn, dev), A)
+    fn, mn = fn.cpu().double(), mn.cpu().numpy()
+    nf = ~terminal
+    # trainer.py:163-187 (every forward in training mode, the next-state forwards on the non-final subset)
+    q_sa = _torch_forward(ref, fs).gather(1, torch.from_numpy(action)[:, None])
+    bias = torch.from_numpy(np.where(mn[nf] != 0, 0.0, -np.inf))
+    nsv = torch.zeros(n, dtype=torch.float64)
+    with torch.no_grad():
+        if double:
+            a_star = (_torch_forward(ref, fn[nf]) + bias).max(1)[1]
+            nsv[torch.from_numpy(nf)] = _torch_forward(tgt, fn[nf]).gather(1, a_star[:, None]).squeeze(1)
+        else:
+            nsv[torch.from_numpy(nf)] = (_torch_forward(tgt, fn[nf]) + bias).max(1)[0]
+    expected = nsv * gamma + torch.from_numpy(reward).double()
+    loss_ref = F.smooth_l1_loss(q_sa, expected[:, None])
+    loss_ref.backward()
+    want = torch.cat([p_.grad.reshape(-1) for p_ in ref.parameters()])
+    loss = tr._update_from_arrays(rs, rn, action, reward, terminal)
+    assert abs(loss - float(loss_ref.detach())) < 2e-6
+    gs = float(want.abs().max())
+    assert float((tr._grad.cpu().double() - want).abs().max()) <= 2e-5 * gs
+    for bm, br, bt, btr in zip(tr.model.bn_layers, ref.bn_layers, tr.target_model.bn_layers, tgt.bn_layers):
+        np.testing.assert_allclose(bm.running_mean.cpu().numpy(), br.running_mean.numpy(), rtol=S_RTOL, atol=S_ATOL)
+        np.testing.assert_allclose(bm.running_var.cpu().numpy(), br.running_var.numpy(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(bt.running_var.cpu().numpy(), btr.running_var.numpy(), rtol=1e-4, atol=1e-5)
+        assert int(bm.num_batches_tracked) == int(br.num_batches_tracked) and int(bt.num_batches_tracked) == 1
+    with pytest.raises(ValueError):  # all transitions terminal: np.stack([]) fails in the reference too (trainer.py:157)
+        tr._update_from_arrays(rs, rn, action, reward, np.ones(n, dtype=bool))
