@@ -270,3 +270,68 @@ def clamp_adam_step(sd: dict, grads: dict, adam_state: dict, lr: float, step: in
         bc2 = 1 - b2 ** step
         denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
         p.addcdiv_(m, denom, value=-(lr / bc1))
+
+
+# ---------------------------------------------------------------------------------------
+# a6 / a8 with bn=True: MLPModel.forward in TRAINING mode (mlp_model.py:12-15,21-30) under Trainer._update.
+# The reference's Trainer never calls .eval() on model / target_model (trainer.py:41-43), so every forward of the update
+# normalises with the statistics of its own batch and moves the running statistics.  BatchNorm1d is written out here
+# (torch/nn/modules/batchnorm.py + F.batch_norm semantics): per channel over (batch, action columns), biased variance
+# for the normalisation, eps 1e-5; running_mean / running_var move by momentum 0.1 towards the batch mean / the
+# UNBIASED batch variance; num_batches_tracked += 1.
+# ---------------------------------------------------------------------------------------
+def mlp_forward_bn_train(sd: dict, x: torch.Tensor, buffers: Optional[dict] = None, momentum: float = 0.1,
+                         eps: float = 1e-5) -> torch.Tensor:
+    """sd: parameters by state_dict key (layers.i.weight (H, C, 1) without bias, bn_layers.i.weight / .bias, output.*);
+    `buffers` (state_dict keys bn_layers.i.running_mean / running_var / num_batches_tracked) is updated in place."""
+    h = x
+    i = 0
+    while f"layers.{i}.weight" in sd:
+        z = torch.einsum("oc,bca->boa", sd[f"layers.{i}.weight"][:, :, 0], h)  # mlp_model.py:23, bias=False (:12)
+        n = z.shape[0] * z.shape[2]
+        mean = z.mean(dim=(0, 2))
+        var = ((z - mean[None, :, None]) ** 2).mean(dim=(0, 2))  # biased
+        if buffers is not None:
+            with torch.no_grad():
+                rm, rv = buffers[f"bn_layers.{i}.running_mean"], buffers[f"bn_layers.{i}.running_var"]
+                rm.mul_(1 - momentum).add_(mean.detach().to(rm.dtype), alpha=momentum)
+                rv.mul_(1 - momentum).add_((var.detach() * (n / max(n - 1, 1))).to(rv.dtype), alpha=momentum)
+                buffers[f"bn_layers.{i}.num_batches_tracked"] += 1
+        xhat = (z - mean[None, :, None]) / torch.sqrt(var[None, :, None] + eps)
+        h = torch.relu(xhat * sd[f"bn_layers.{i}.weight"][None, :, None] + sd[f"bn_layers.{i}.bias"][None, :, None])  # :24-27
+        i += 1
+    out = torch.einsum("oc,bca->boa", sd["output.weight"][:, :, 0], h) + sd["output.bias"][None, :, None]  # :28
+    return out.reshape(out.shape[0], -1)  # :29
+
+
+def dqn_update_grads_bn(sd: dict, target_sd: dict, state: np.ndarray, action: np.ndarray, reward: np.ndarray,
+                        next_state: np.ndarray, next_mask: np.ndarray, non_final: np.ndarray, gamma: float,
+                        double_dqn: bool = True, dtype=torch.float32):
+    """dqn_update_grads for a bn=True network.  sd / target_sd: FULL state_dicts (parameters and BatchNorm buffers);
+    their buffers move as the reference's do: the online network's once for model(state_batch) (trainer.py:163) and once
+    more for model(non_final_next_states) under Double DQN (:174), the target's once (:175 / :182).
+    Returns (loss, grads of the parameters before the clamp)."""
+    is_param = lambda k: not (k.endswith("running_mean") or k.endswith("running_var") or k.endswith("num_batches_tracked"))
+    params = {k: v.detach().clone().to(dtype).requires_grad_(True) for k, v in sd.items() if is_param(k)}
+    tparams = {k: v.detach().to(dtype) for k, v in target_sd.items() if is_param(k)}
+    nf = np.asarray(non_final, dtype=bool)
+    s = torch.from_numpy(state).to(dtype)
+    a = torch.from_numpy(np.asarray(action, dtype=np.int64)[:, None])
+    r = torch.from_numpy(np.asarray(reward, dtype=np.float32)).to(dtype)
+    q_sa = mlp_forward_bn_train(params, s, sd).gather(1, a)  # :163
+    ns = torch.from_numpy(next_state[nf]).to(dtype)  # :157-158: np.stack([]) raises when every transition is terminal
+    if ns.shape[0] == 0:
+        raise ValueError("need at least one array to stack")
+    bias = torch.from_numpy(np.where(next_mask[nf], 0.0, -np.inf)).to(dtype)  # :169-170
+    v_next = torch.zeros(state.shape[0], dtype=dtype)
+    with torch.no_grad():
+        if double_dqn:  # :171-177
+            a_star = (mlp_forward_bn_train({k: p.detach() for k, p in params.items()}, ns, sd) + bias).max(1)[1]
+            v = mlp_forward_bn_train(tparams, ns, target_sd).gather(1, a_star.unsqueeze(1)).squeeze(1)
+        else:  # :178-182
+            v = (mlp_forward_bn_train(tparams, ns, target_sd) + bias).max(1)[0]
+    v_next[torch.from_numpy(nf)] = v
+    y = v_next * gamma + r  # :184
+    loss = F.smooth_l1_loss(q_sa, y.unsqueeze(1))  # :187
+    loss.backward()  # :192
+    return float(loss.detach()), {k: p.grad.detach().clone() for k, p in params.items()}

@@ -300,3 +300,50 @@ def test_bn_update_tiny_batches_match_torch(tables, n, term, double):
         assert int(bm.num_batches_tracked) == int(br.num_batches_tracked) and int(bt.num_batches_tracked) == 1
     with pytest.raises(ValueError):  # all transitions terminal: np.stack([]) fails in the reference too (trainer.py:157)
         tr._update_from_arrays(rs, rn, action, reward, np.ones(n, dtype=bool))
+
+
+@pytest.mark.parametrize("n,ps,nl,H,double", [(300, 6, 2, 64, True), (129, 2, 3, 32, False)])
+def test_bn_update_matches_oracle(tables, n, ps, nl, H, double):
+    """Trainer's bn update against the oracle's written-out restatement (oracle/ref_port.py::dqn_update_grads_bn, itself
+    pinned to the reference's golden vectors by tests/test_oracle.py) evaluated in float64, on seeded synthetic transitions:
+    loss, pre-clamp gradient, running statistics and counters of both networks."""
+    from oracle import packed_oracle, ref_port
+    from pokeai_b200.mlp_model import MLPModel
+    from pokeai_b200.packed import synth_packed
+    from pokeai_b200.trainer import Trainer
+    A = 4 + ps - 1
+    torch.manual_seed(1000 + n)
+    tr = Trainer({"n_layers": nl, "n_channels": H, "bn": True}, {"batch_size": n, "gamma": 0.95, "double_dqn": double},
+                 {"party_size": ps}, device=DEV)
+    protos = [MLPModel((tables.n_channels, A), A, n_layers=nl, n_channels=H, bn=True) for _ in range(2)]
+    with torch.no_grad():
+        for m_ in protos:
+            for b in m_.bn_layers:
+                b.weight.uniform_(0.5, 1.5)
+                b.bias.normal_(0, 0.1)
+                b.running_mean.normal_(0, 0.2)
+                b.running_var.uniform_(0.5, 1.5)
+    tr.model.load_state_dict(protos[0].state_dict())
+    tr.target_model.load_state_dict(protos[1].state_dict())
+    sd = {k: v.detach().clone().double() if v.is_floating_point() else v.clone() for k, v in protos[0].state_dict().items()}
+    tgt = {k: v.detach().clone().double() if v.is_floating_point() else v.clone() for k, v in protos[1].state_dict().items()}
+    rs = synth_packed(n, seed=n, party_size=ps, kind="ragged", tables=tables)
+    rn = synth_packed(n, seed=n + 1, party_size=ps, kind="ragged", tables=tables)
+    rng = np.random.default_rng(n)
+    action = (rng.random(n) * rs["n_act"]).astype(np.int64)
+    reward = rng.uniform(-2, 2, n).astype(np.float32)
+    terminal = rng.random(n) < 0.1
+    fs, _ = packed_oracle.encode(rs, ps, tables)
+    fn, mn = packed_oracle.encode(rn, ps, tables)
+    loss_o, grads_o = ref_port.dqn_update_grads_bn(sd, tgt, fs, action, reward, fn, mn, ~terminal, 0.95, double_dqn=double,
+                                                   dtype=torch.float64)
+    loss = tr._update_from_arrays(rs, rn, action, reward, terminal)
+    assert abs(loss - loss_o) < 2e-6
+    want = torch.cat([grads_o[k].reshape(-1) for k, _ in tr.model.named_parameters()])
+    assert float((tr._grad.cpu().double() - want).abs().max()) <= 2e-5 * float(want.abs().max())
+    for which, mine, theirs in (("online", tr.model.state_dict(), sd), ("target", tr.target_model.state_dict(), tgt)):
+        for k, v in theirs.items():
+            if k.endswith("num_batches_tracked"):
+                assert int(mine[k]) == int(v), (which, k)
+            elif k.endswith(("running_mean", "running_var")):
+                np.testing.assert_allclose(mine[k].cpu().numpy(), v.numpy(), rtol=1e-5, atol=1e-6, err_msg=f"{which} {k}")

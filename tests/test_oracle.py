@@ -110,6 +110,53 @@ def test_dqn_update_port_matches_reference(tables):
             np.testing.assert_allclose(p.numpy(), z[f"sd{step}_{k}"], rtol=1e-6, atol=1e-7)
 
 
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_bn_update_port_matches_reference(tables, tag):
+    """The written-out train-mode BatchNorm update (ref_port.dqn_update_grads_bn) against the real reference's
+    Trainer._update with bn: true (tools/make_golden_bn.py): loss, pre-clamp gradients, running statistics and counters
+    of both networks, and the parameters after clamp + Adam wherever the step is well conditioned (|g| >= 1e-6: at the
+    first steps Adam moves a weight by lr * g / (|g| + 1e-8), so a gradient that is zero up to rounding gives a step
+    that is noise in any implementation, torch's own included)."""
+    z = np.load(GOLDEN / "dqn_update_bn.npz")
+    p = tag + "_"
+    ps = int(z[p + "party_size"])
+    rec_s = np.frombuffer(z[p + "packed_s"].tobytes(), dtype=PK_OBS_DTYPE)
+    rec_n = np.frombuffer(z[p + "packed_n"].tobytes(), dtype=PK_OBS_DTYPE)
+    fs, _ = packed_oracle.encode(rec_s, ps, tables)
+    fn, mn = packed_oracle.encode(rec_n, ps, tables)
+    sd = {k: v.clone() for k, v in _sd(z, p + "sd0_").items()}
+    tgt = {k: v.clone() for k, v in _sd(z, p + "tgt0_").items()}
+    is_param = lambda k: not k.endswith(("running_mean", "running_var", "num_batches_tracked"))
+    adam = {}
+    shaky = {}
+    for step in (1, 2):
+        loss, grads = ref_port.dqn_update_grads_bn(sd, tgt, fs, z[p + "action"], z[p + "reward"], fn, mn, ~z[p + "terminal"],
+                                                   float(z[p + "gamma"]), double_dqn=bool(z[p + "double_dqn"]))
+        assert abs(loss - float(z[f"{p}loss{step}"])) < 1e-6
+        for k, g in grads.items():
+            want = z[f"{p}grad{step}_{k}"]
+            np.testing.assert_allclose(g.numpy(), want, rtol=1e-4, atol=2e-7, err_msg=k)
+            shaky[k] = shaky.get(k, False) | ((np.abs(want) < 1e-6) & (want != 0))
+        params = {k: v for k, v in sd.items() if is_param(k)}
+        ref_port.clamp_adam_step(params, grads, adam, float(z[p + "lr"]), step)
+        for k, v in sd.items():
+            want = z[f"{p}sd{step}_{k}"]
+            if k.endswith("num_batches_tracked"):
+                assert int(v) == int(want), k
+            elif is_param(k):
+                ok = ~shaky[k]
+                np.testing.assert_allclose(v.numpy()[ok], want[ok], rtol=1e-5, atol=2e-6, err_msg=k)
+            else:
+                np.testing.assert_allclose(v.numpy(), want, rtol=1e-5, atol=1e-6, err_msg=k)
+        for k, v in tgt.items():
+            if "bn_layers" in k and not is_param(k):
+                want = z[f"{p}tgt{step}_{k}"]
+                if k.endswith("num_batches_tracked"):
+                    assert int(v) == int(want), k
+                else:
+                    np.testing.assert_allclose(v.numpy(), want, rtol=1e-5, atol=1e-6, err_msg="target " + k)
+
+
 def test_select_restatements():
     rng = np.random.default_rng(0)
     q = rng.standard_normal((64, 9)).astype(np.float32)
