@@ -233,3 +233,39 @@ def test_policy_on_gpu_matches_object_route(cases, statuses, tables):
     single = [p.choice_turn_start(b, r) for p, b, r in zip(pols, bss, reqs)]
     assert single == want
     assert PackedRLPolicy.choice_batch(pols, bss, reqs) == want
+
+
+@pytest.mark.parametrize("party_size", [1, 2, 3, 4, 5, 6])
+def test_packers_agree_on_seeded_synthetic_requests(tables, party_size):
+    """Wider than the 240 golden cases: 400 seeded (battle_status, request) pairs per party size from the lock-step
+    driver's generator (forced switches, trapped, disabled moves, fainted bench, every rank / weather / condition) --
+    pack_request (numpy fields), pack_request_into_py (struct) and csrc/pkpack.c give the same bytes and keys, and the
+    record decodes through the packed oracle to the features of the object route."""
+    import random
+    from oracle import packed_oracle as PO
+    from pokeai_b200 import build as b
+    from pokeai_b200 import protocol as P
+    from pokeai_b200.lockstep import synthetic_battle_status, synthetic_request
+    from pokeai_b200.packed import PK_OBS_BYTES
+    cpack = P._load_c_packer() if b.build_packer() is not None else None
+    rng = random.Random(1000 + party_size)
+    recs = []
+    for i in range(400):
+        bs = synthetic_battle_status(rng, tables, party_size)
+        req = synthetic_request(rng, tables, party_size)
+        rec, keys = P.pack_request(bs, req, tables)
+        b1 = bytearray(b"\x55" * PK_OBS_BYTES)
+        assert P.pack_request_into_py(b1, 0, bs, req, tables) == keys, i
+        assert bytes(b1) == rec.tobytes(), i
+        if cpack is not None:
+            b2 = bytearray(b"\x55" * PK_OBS_BYTES)
+            k2 = cpack(b2, 0, bs, req, tables.species_name_to_idx, tables.move_to_idx, tables.item_to_idx, 9,
+                       P.STATUS_CODE, P.STATUS_FNT, P.WEATHER_CODE)
+            assert k2 == keys and b2 == b1, i
+        assert 1 <= len(keys) <= 9 and int(np.atleast_1d(rec)["n_act"][0]) == len(keys)
+        recs.append(rec)
+    # the records are well formed for the decision path: the packed oracle encodes them, the mask is the action count
+    packed = np.concatenate([np.atleast_1d(r) for r in recs])
+    feats, mask = PO.encode(packed, 6, tables)
+    assert feats.shape == (400, tables.n_channels, 9) and np.isfinite(feats).all()
+    assert (mask.sum(axis=1) == packed["n_act"]).all()
