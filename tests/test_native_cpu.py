@@ -20,6 +20,14 @@ def test_library_builds_loads_and_exports_header():
     assert lib.pk_abi_version() == 1
 
 
+def test_every_entry_point_is_mapped_to_the_reference_in_integration_md():
+    """INTEGRATION.md's entry point table names every symbol the header declares (beside what it replaces)"""
+    from pathlib import Path
+    from pokeai_b200 import _native as N
+    text = (Path(__file__).resolve().parents[1] / "INTEGRATION.md").read_text()
+    assert [s for s in N.declared_symbols() if s not in text] == []
+
+
 def test_layout_sizes():
     from pokeai_b200 import _native as N
     lib = N.lib()
