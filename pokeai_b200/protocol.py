@@ -262,6 +262,15 @@ class PackedRLPolicy:
 
     def _calc_reward_potential(self, battle_status) -> float:
         c = self.surrogate_reward_config
+        if c.hp_ratio == 0.0 and c.alive_ratio == 0.0:
+            # every term off (the default of surrogate_reward_config.py:4-15, and what rating battles use): both sides'
+            # sums are x * 0.0 + y * 0.0 = 0.0 for any state, so the potential is 0.0 (-0.0 with only_opponent) and the
+            # walk over the reserve members is skipped; the state checks of get_mean_hp_ratio stay
+            sides = battle_status.side_statuses
+            f, o = sides[battle_status.side_friend], sides[battle_status.side_opponent]
+            assert f.total_pokes > 0 and o.total_pokes > 0
+            assert f.active is not None and o.active is not None
+            return -0.0 if c.only_opponent else 0.0
         sps = []
         for side in (battle_status.side_friend, battle_status.side_opponent):  # rl_policy.py:66-70
             ss = battle_status.side_statuses[side]

@@ -204,6 +204,29 @@ def test_policy_rewards_and_single_choice(cases, statuses, tables):
     assert pol2.last_reward_potential == pytest.approx(-0.25)
 
 
+def test_reward_potential_with_every_term_off_is_the_general_formula(statuses, tables):
+    """the short cut for hp_ratio == alive_ratio == 0 returns the bits (sign of zero included) of rl_policy.py:60-74's
+    formula, and keeps its state checks"""
+    import struct
+    from pokeai_b200.protocol import PackedRLPolicy
+    agent = _FakeAgent(9)
+    for only_opponent in (False, True):
+        c = Cfg(0.0, 0.0, only_opponent, False)
+        pol = PackedRLPolicy(agent, c, tables)
+        for bs in statuses[:50]:
+            sps = [ss.get_mean_hp_ratio() * c.hp_ratio + ss.get_alive_ratio() * c.alive_ratio
+                   for ss in (bs.side_statuses[bs.side_friend], bs.side_statuses[bs.side_opponent])]
+            want = -sps[1] if only_opponent else sps[0] - sps[1]
+            assert struct.pack("d", pol._calc_reward_potential(bs)) == struct.pack("d", want)
+    bad = copy.copy(statuses[0])
+    bad.side_statuses = dict(bad.side_statuses)
+    broken = copy.copy(bad.side_statuses[bad.side_opponent])
+    broken.total_pokes = 0
+    bad.side_statuses[bad.side_opponent] = broken
+    with pytest.raises(AssertionError):
+        pol._calc_reward_potential(bad)
+
+
 @pytest.mark.gpu
 def test_policy_on_gpu_matches_object_route(cases, statuses, tables):
     """PackedRLPolicy (single calls and choice_batch) picks what AgentVal.act picks on the reference-style
