@@ -58,3 +58,27 @@ def test_reference_arm_of_the_bench_runs_the_reference(R, tables):
     rec = synth_packed(64, seed=0, party_size=6, kind="full", tables=tables)
     step, kind = bench.cpu_decide_factory(rec, 2, 64, 1)
     assert kind == "reference" and step(64) == 64
+
+
+def test_reference_arm_under_torchrun_prints_one_line_from_rank_0(R):
+    """`bench.py --impl reference --gpus 2` launched as the driver launches it (one process per GPU): rank 0 alone
+    runs the CPU arm and prints ONE JSON line, the other rank exits 0 without work; no GPU is touched"""
+    import json
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29571", "bench.py", "--impl", "reference",
+                        "--gpus", "2", "--steps", "1", "--warmup", "1"], cwd=root, env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [json.loads(x) for x in p.stdout.splitlines() if x.startswith("{")]
+    assert len(lines) == 1
+    d = lines[0]
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    assert d["value"] > 0 and d["higher_is_better"] is True
